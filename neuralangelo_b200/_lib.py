@@ -1,0 +1,101 @@
+"""ctypes binding of libna_b200.so (the C ABI declared in include/na_b200.h).
+
+The product path has no CPU or eager-PyTorch fallback: if the library cannot be
+loaded, or a call fails, an exception is raised.
+"""
+import ctypes
+import os
+
+import torch
+
+_PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG_DIR, "libna_b200.so")
+
+NA_MAX_LEVELS = 32
+
+c_f32p = ctypes.POINTER(ctypes.c_float)
+
+
+class HashGridDesc(ctypes.Structure):
+    """Mirror of `na_hashgrid_desc` (include/na_b200.h)."""
+    _fields_ = [
+        ("n_levels", ctypes.c_uint32),
+        ("n_features", ctypes.c_uint32),
+        ("total_entries", ctypes.c_uint32),
+        ("reserved", ctypes.c_uint32),
+        ("scale", ctypes.c_float * NA_MAX_LEVELS),
+        ("resolution", ctypes.c_uint32 * NA_MAX_LEVELS),
+        ("entries", ctypes.c_uint32 * NA_MAX_LEVELS),
+        ("offset", ctypes.c_uint32 * NA_MAX_LEVELS),
+        ("hashed", ctypes.c_uint32 * NA_MAX_LEVELS),
+    ]
+
+
+class UnitMap(ctypes.Structure):
+    """Mirror of `na_unit_map`."""
+    _fields_ = [("vol_min", ctypes.c_float), ("inv_extent", ctypes.c_float)]
+
+
+class NaError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def _declare(lib):
+    vp, i64, u32, f32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_uint32, ctypes.c_float
+    descp = ctypes.POINTER(HashGridDesc)
+    sig = {
+        "na_abi_version": (ctypes.c_int, []),
+        "na_last_error": (ctypes.c_char_p, []),
+        "na_hashgrid_make_desc": (ctypes.c_int, [u32, u32, u32, u32, ctypes.c_double, descp]),
+        "na_hashgrid_fwd": (ctypes.c_int, [descp, vp, vp, i64, UnitMap, u32, vp, i64, vp]),
+        "na_hashgrid_bwd": (ctypes.c_int, [descp, vp, i64, UnitMap, u32, vp, i64, vp, vp]),
+        "na_hashgrid_taps_fwd": (ctypes.c_int, [descp, vp, vp, i64, UnitMap, u32, c_f32p, u32, vp, i64, i64, vp]),
+        "na_hashgrid_taps_bwd": (ctypes.c_int, [descp, vp, i64, UnitMap, u32, c_f32p, u32, vp, i64, i64, vp, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    return sig
+
+
+def lib():
+    """Load (once) and return the ctypes handle; raises if the library is missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise NaError(
+                f"{LIB_PATH} not found: build it with `python -m neuralangelo_b200.build` "
+                "(there is no CPU/eager fallback for the CUDA path)")
+        handle = ctypes.CDLL(LIB_PATH)
+        _declare(handle)
+        _lib = handle
+    return _lib
+
+
+def exported_signatures():
+    """Names bound from the library (used by the ABI test)."""
+    return sorted(_declare(lib()).keys())
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().na_last_error().decode("utf-8", "replace")
+        raise NaError(f"{what} failed (code {rc}): {msg}")
+
+
+def current_stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t):
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise NaError("libna_b200 kernels need CUDA tensors; there is no CPU fallback")

@@ -1,0 +1,67 @@
+// Shared helpers for libna_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include "na_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libna_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace na {
+
+void set_error(const char* fmt, ...);
+void clear_error();
+
+constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+
+inline int check_cuda(cudaError_t e, const char* what) {
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return NA_ERR_CUDA;
+    }
+    return NA_OK;
+}
+
+#define NA_REQUIRE(cond, ...)          \
+    do {                               \
+        if (!(cond)) {                 \
+            na::set_error(__VA_ARGS__); \
+            return NA_ERR_INVALID;     \
+        }                              \
+    } while (0)
+
+#define NA_CHECK_LAUNCH(name)                                         \
+    do {                                                              \
+        int _rc = na::check_cuda(cudaGetLastError(), name " launch"); \
+        if (_rc) return _rc;                                          \
+    } while (0)
+
+__device__ __forceinline__ float4 ldg_f4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+// Streaming (touch-once) vector accesses: keep them out of L1 so the table rows stay cached.
+__device__ __forceinline__ float4 ld_stream_f4(const float* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_stream_f4(float* p, float4 v) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+                 "f"(v.w)
+                 : "memory");
+}
+// 16-byte vector reduction (sm_90+): one L2 atomic transaction for 4 floats.
+__device__ __forceinline__ void red_add_f4(float* p, float4 v) {
+    asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+                 "f"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ void red_add_f2(float* p, float2 v) {
+    asm volatile("red.relaxed.gpu.global.add.v2.f32 [%0], {%1,%2};" ::"l"(p), "f"(v.x), "f"(v.y) : "memory");
+}
+
+}  // namespace na
