@@ -19,6 +19,7 @@
 //     vector reduction (red.global.add.v4.f32) per corner instead of one per tap.
 #include "na_common.cuh"
 #include <math.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -116,9 +117,30 @@ struct Vec<4> {
         }
     }
     static __device__ __forceinline__ void red(float* p, float4 v) { na::red_add_f4(p, v); }
+    static __device__ __forceinline__ float4 load_keep(const float* p, uint64_t pol) { return na::ldg_f4_hint(p, pol); }
+    static __device__ __forceinline__ void red_keep(float* p, float4 v, uint64_t pol) { na::red_add_f4_hint(p, v, pol); }
+    template <bool ALIGNED>
+    static __device__ __forceinline__ void store_stream(float* p, float4 v, uint64_t pol) {
+        if (ALIGNED) {
+            na::st_f4_hint(p, v, pol);
+        } else {
+            p[0] = v.x, p[1] = v.y, p[2] = v.z, p[3] = v.w;
+        }
+    }
+    template <bool ALIGNED>
+    static __device__ __forceinline__ float4 load_stream_hint(const float* p, uint64_t pol) {
+        if (ALIGNED) return na::ldg_f4_stream_hint(p, pol);
+        return make_float4(__ldg(p), __ldg(p + 1), __ldg(p + 2), __ldg(p + 3));
+    }
 };
 template <>
 struct Vec<2> {
+    static __device__ __forceinline__ float4 load_keep(const float* p, uint64_t) { return load(p); }
+    static __device__ __forceinline__ void red_keep(float* p, float4 v, uint64_t) { red(p, v); }
+    template <bool ALIGNED>
+    static __device__ __forceinline__ void store_stream(float* p, float4 v, uint64_t) { store<ALIGNED>(p, v); }
+    template <bool ALIGNED>
+    static __device__ __forceinline__ float4 load_stream_hint(const float* p, uint64_t) { return load_stream<ALIGNED>(p); }
     static __device__ __forceinline__ float4 load(const float* p) {
         float2 t = __ldg(reinterpret_cast<const float2*>(p));
         return make_float4(t.x, t.y, 0.f, 0.f);
@@ -146,124 +168,236 @@ struct Shape {
 };
 
 // ---------------------------------------------------------------------------------------------
-// forward (n_taps evaluations per point; tap 0 is the reference cell whose corners are cached)
+// Thread mapping (both directions): one warp walks whole feature rows.  Lane -> (point-in-warp,
+// level, 16-byte feature slice); for the default 16 levels x 8 features a warp is exactly one
+// point: lanes (2l, 2l+1) own level l, so every output / dout access of the warp is one
+// contiguous 512-byte row (full 128-byte lines to HBM instead of lone 32-byte sectors) and the
+// point's coordinates are a broadcast load.  A CTA owns a contiguous run of points and its warps
+// interleave over it, so spatially coherent inputs (samples along a ray) re-use table rows in L1.
 // ---------------------------------------------------------------------------------------------
+struct Mapping {
+    int lanes_per_level;   // F / V
+    int levels_per_pass;   // levels handled by one warp pass
+    int points_per_warp;   // >1 only when n_levels * lanes_per_level <= 16
+    int passes;            // ceil(n_levels / levels_per_pass)
+    int points_per_cta;
+};
+
+struct LevelS {
+    float scale;
+    uint32_t res, entries, hashed, pow2mask, offset;
+};
+
+__device__ __forceinline__ void stage_levels(const na_hashgrid_desc& desc, LevelS* sl) {
+    if (threadIdx.x < desc.n_levels) {
+        const uint32_t l = threadIdx.x;
+        LevelS v;
+        v.scale = desc.scale[l];
+        v.res = desc.resolution[l];
+        v.entries = desc.entries[l];
+        v.hashed = desc.hashed[l];
+        v.pow2mask = ((v.entries & (v.entries - 1u)) == 0u) ? (v.entries - 1u) : 0u;
+        v.offset = desc.offset[l];
+        sl[l] = v;
+    }
+    __syncthreads();
+}
+
+template <int F>
+__device__ __forceinline__ Level make_level(const LevelS& v, const float* table) {
+    Level L;
+    L.scale = v.scale;
+    L.res = v.res;
+    L.entries = v.entries;
+    L.hashed = v.hashed;
+    L.pow2mask = v.pow2mask;
+    L.base = table + (size_t)v.offset * F;
+    return L;
+}
+
+__device__ __forceinline__ Cell locate_tap(const Level& L, const na_unit_map& map, const TapParams& taps, uint32_t t,
+                                           float x0, float x1, float x2) {
+    return locate(L, (x0 + taps.off[t][0] - map.vol_min) * map.inv_extent,
+                  (x1 + taps.off[t][1] - map.vol_min) * map.inv_extent,
+                  (x2 + taps.off[t][2] - map.vol_min) * map.inv_extent);
+}
+
+__device__ __forceinline__ bool same_cell(const Cell& a, const Cell& b) {
+    return a.gx == b.gx && a.gy == b.gy && a.gz == b.gz;
+}
+
 template <int F, bool ALIGNED>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 3)
 hashgrid_taps_fwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ table,
                          const float* __restrict__ x, int64_t n_points, na_unit_map map, uint32_t active_levels,
                          const __grid_constant__ TapParams taps, float* __restrict__ out, int64_t out_stride,
-                         int64_t out_tap_stride) {
+                         int64_t out_tap_stride, const Mapping m) {
     using S = Shape<F>;
     using VT = Vec<S::V>;
-    const uint32_t level = blockIdx.y;
-    const int64_t n = (int64_t)blockIdx.x * S::PTS + threadIdx.x / S::LPP;
-    const int sub = threadIdx.x % S::LPP;
-    if (n >= n_points) return;
-    float* o = out + n * out_stride + level * F + sub * S::V;
-    if (level >= active_levels) {  // coarse-to-fine mask: inactive levels are exactly zero
-        for (uint32_t t = 0; t < taps.n; ++t)
-            VT::template store<ALIGNED>(o + t * out_tap_stride, make_float4(0.f, 0.f, 0.f, 0.f));
-        return;
-    }
-    const Level L = load_level<F>(desc, level, table);
+    __shared__ LevelS sl[NA_MAX_LEVELS];
+    stage_levels(desc, sl);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % S::LPP;
+    const int lvl_in_pass = (lane / S::LPP) % m.levels_per_pass;
+    const int pt_in_warp = lane / (S::LPP * m.levels_per_pass);
+    const uint32_t level = blockIdx.y * m.levels_per_pass + lvl_in_pass;
+    if (pt_in_warp >= m.points_per_warp || level >= desc.n_levels) return;
+    const bool active = level < active_levels;
+    const Level L = make_level<F>(sl[level], table);
     const float* tb = L.base + sub * S::V;
-    const float x0 = __ldg(x + n * 3 + 0), x1 = __ldg(x + n * 3 + 1), x2 = __ldg(x + n * 3 + 2);
+    const uint64_t keep = na::policy_evict_last(), stream = na::policy_evict_first();
+    const int64_t cta_base = (int64_t)blockIdx.x * m.points_per_cta;
+    const int step = (kThreads / 32) * m.points_per_warp;
 
-    // tap 0: gather the 8 corner rows and keep them.
-    const Cell c0 = locate(L, (x0 + taps.off[0][0] - map.vol_min) * map.inv_extent,
-                           (x1 + taps.off[0][1] - map.vol_min) * map.inv_extent,
-                           (x2 + taps.off[0][2] - map.vol_min) * map.inv_extent);
-    float4 corner[8];
+    for (int i = warp * m.points_per_warp + pt_in_warp; i < m.points_per_cta; i += step) {
+        const int64_t n = cta_base + i;
+        if (n >= n_points) break;
+        float* o = out + n * out_stride + level * F + sub * S::V;
+        if (!active) {  // coarse-to-fine mask: inactive levels are exactly zero
+            for (uint32_t t = 0; t < taps.n; ++t)
+                VT::template store_stream<ALIGNED>(o + t * out_tap_stride, make_float4(0.f, 0.f, 0.f, 0.f), stream);
+            continue;
+        }
+        const float x0 = __ldg(x + n * 3 + 0), x1 = __ldg(x + n * 3 + 1), x2 = __ldg(x + n * 3 + 2);
+        // tap 0: gather the 8 corner rows of its cell and keep them in registers.
+        const Cell c0 = locate_tap(L, map, taps, 0, x0, x1, x2);
+        float4 corner[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        uint32_t idx = entry_index(L, c0.gx + (k & 1), c0.gy + ((k >> 1) & 1), c0.gz + ((k >> 2) & 1));
-        corner[k] = VT::load(tb + (size_t)idx * F);
-    }
-    {
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = 0; k < 8; ++k) {
+            const uint32_t idx = entry_index(L, c0.gx + (k & 1), c0.gy + ((k >> 1) & 1), c0.gz + ((k >> 2) & 1));
+            corner[k] = VT::load_keep(tb + (size_t)idx * F, keep);
+        }
+        {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) axpy4(acc, corner_weight(c0, k), corner[k]);
-        VT::template store<ALIGNED>(o, acc);
-    }
+            for (int k = 0; k < 8; ++k) axpy4(acc, corner_weight(c0, k), corner[k]);
+            VT::template store_stream<ALIGNED>(o, acc, stream);
+        }
+        // taps that stay in tap 0's cell re-use the cached rows; the others are remembered in `pending`.
+        uint32_t pending = 0;
 #pragma unroll 1
-    for (uint32_t t = 1; t < taps.n; ++t) {
-        const Cell c = locate(L, (x0 + taps.off[t][0] - map.vol_min) * map.inv_extent,
-                              (x1 + taps.off[t][1] - map.vol_min) * map.inv_extent,
-                              (x2 + taps.off[t][2] - map.vol_min) * map.inv_extent);
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (c.gx == c0.gx && c.gy == c0.gy && c.gz == c0.gz) {
+        for (uint32_t t = 1; t < taps.n; ++t) {
+            const Cell c = locate_tap(L, map, taps, t, x0, x1, x2);
+            if (same_cell(c, c0)) {
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) axpy4(acc, corner_weight(c, k), corner[k]);
-        } else {
+                for (int k = 0; k < 8; ++k) axpy4(acc, corner_weight(c, k), corner[k]);
+                VT::template store_stream<ALIGNED>(o + t * out_tap_stride, acc, stream);
+            } else {
+                pending |= 1u << t;
+            }
+        }
+        // cell-crossing taps: every lane works through its own list, so the warp needs
+        // max(#crossing taps per lane) gather rounds rather than one per tap index.
+        while (pending) {
+            const uint32_t t = __ffs(pending) - 1;
+            pending &= pending - 1;
+            const Cell c = locate_tap(L, map, taps, t, x0, x1, x2);
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
             float4 v[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-                uint32_t idx = entry_index(L, c.gx + (k & 1), c.gy + ((k >> 1) & 1), c.gz + ((k >> 2) & 1));
-                v[k] = VT::load(tb + (size_t)idx * F);
+                const uint32_t idx = entry_index(L, c.gx + (k & 1), c.gy + ((k >> 1) & 1), c.gz + ((k >> 2) & 1));
+                v[k] = VT::load_keep(tb + (size_t)idx * F, keep);
             }
 #pragma unroll
             for (int k = 0; k < 8; ++k) axpy4(acc, corner_weight(c, k), v[k]);
+            VT::template store_stream<ALIGNED>(o + t * out_tap_stride, acc, stream);
         }
-        VT::template store<ALIGNED>(o + t * out_tap_stride, acc);
     }
 }
 
 // ---------------------------------------------------------------------------------------------
-// backward: scatter-add into the table gradient
+// backward: scatter-add into the table gradient (same mapping; grid.y covers active levels only)
 // ---------------------------------------------------------------------------------------------
 template <int F, bool ALIGNED>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 3)
 hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ x,
                          int64_t n_points, na_unit_map map, uint32_t active_levels,
                          const __grid_constant__ TapParams taps, const float* __restrict__ dout,
-                         int64_t dout_stride, int64_t dout_tap_stride, float* __restrict__ dtable) {
+                         int64_t dout_stride, int64_t dout_tap_stride, float* __restrict__ dtable, const Mapping m) {
     using S = Shape<F>;
     using VT = Vec<S::V>;
-    const uint32_t level = blockIdx.y;  // grid.y == active levels only
-    const int64_t n = (int64_t)blockIdx.x * S::PTS + threadIdx.x / S::LPP;
-    const int sub = threadIdx.x % S::LPP;
-    if (n >= n_points) return;
-    const Level L = load_level<F>(desc, level, dtable);
+    __shared__ LevelS sl[NA_MAX_LEVELS];
+    stage_levels(desc, sl);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % S::LPP;
+    const int lvl_in_pass = (lane / S::LPP) % m.levels_per_pass;
+    const int pt_in_warp = lane / (S::LPP * m.levels_per_pass);
+    const uint32_t level = blockIdx.y * m.levels_per_pass + lvl_in_pass;
+    if (pt_in_warp >= m.points_per_warp || level >= active_levels) return;
+    const Level L = make_level<F>(sl[level], dtable);
     float* tb = const_cast<float*>(L.base) + sub * S::V;
-    const float* g = dout + n * dout_stride + level * F + sub * S::V;
-    const float x0 = __ldg(x + n * 3 + 0), x1 = __ldg(x + n * 3 + 1), x2 = __ldg(x + n * 3 + 2);
+    const uint64_t keep = na::policy_evict_last(), stream = na::policy_evict_first();
+    const int64_t cta_base = (int64_t)blockIdx.x * m.points_per_cta;
+    const int step = (kThreads / 32) * m.points_per_warp;
 
-    const Cell c0 = locate(L, (x0 + taps.off[0][0] - map.vol_min) * map.inv_extent,
-                           (x1 + taps.off[0][1] - map.vol_min) * map.inv_extent,
-                           (x2 + taps.off[0][2] - map.vol_min) * map.inv_extent);
-    float4 acc[8];
-    {
-        const float4 d = VT::template load_stream<ALIGNED>(g);
+    for (int i = warp * m.points_per_warp + pt_in_warp; i < m.points_per_cta; i += step) {
+        const int64_t n = cta_base + i;
+        if (n >= n_points) break;
+        const float* g = dout + n * dout_stride + level * F + sub * S::V;
+        const float x0 = __ldg(x + n * 3 + 0), x1 = __ldg(x + n * 3 + 1), x2 = __ldg(x + n * 3 + 2);
+        const Cell c0 = locate_tap(L, map, taps, 0, x0, x1, x2);
+        float4 acc[8];
+        {
+            const float4 d = VT::template load_stream_hint<ALIGNED>(g, stream);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float w = corner_weight(c0, k);
+                acc[k] = make_float4(w * d.x, w * d.y, w * d.z, w * d.w);
+            }
+        }
+        uint32_t pending = 0;
+#pragma unroll 1
+        for (uint32_t t = 1; t < taps.n; ++t) {
+            const Cell c = locate_tap(L, map, taps, t, x0, x1, x2);
+            if (same_cell(c, c0)) {  // pre-sum: one reduction per corner for all taps of this cell
+                const float4 d = VT::template load_stream_hint<ALIGNED>(g + t * dout_tap_stride, stream);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) axpy4(acc[k], corner_weight(c, k), d);
+            } else {
+                pending |= 1u << t;
+            }
+        }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            const float w = corner_weight(c0, k);
-            acc[k] = make_float4(w * d.x, w * d.y, w * d.z, w * d.w);
+            const uint32_t idx = entry_index(L, c0.gx + (k & 1), c0.gy + ((k >> 1) & 1), c0.gz + ((k >> 2) & 1));
+            VT::red_keep(tb + (size_t)idx * F, acc[k], keep);
         }
-    }
-#pragma unroll 1
-    for (uint32_t t = 1; t < taps.n; ++t) {
-        const Cell c = locate(L, (x0 + taps.off[t][0] - map.vol_min) * map.inv_extent,
-                              (x1 + taps.off[t][1] - map.vol_min) * map.inv_extent,
-                              (x2 + taps.off[t][2] - map.vol_min) * map.inv_extent);
-        const float4 d = VT::template load_stream<ALIGNED>(g + t * dout_tap_stride);
-        if (c.gx == c0.gx && c.gy == c0.gy && c.gz == c0.gz) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) axpy4(acc[k], corner_weight(c, k), d);
-        } else {
+        while (pending) {
+            const uint32_t t = __ffs(pending) - 1;
+            pending &= pending - 1;
+            const Cell c = locate_tap(L, map, taps, t, x0, x1, x2);
+            const float4 d = VT::template load_stream_hint<ALIGNED>(g + t * dout_tap_stride, stream);
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const float w = corner_weight(c, k);
-                uint32_t idx = entry_index(L, c.gx + (k & 1), c.gy + ((k >> 1) & 1), c.gz + ((k >> 2) & 1));
-                VT::red(tb + (size_t)idx * F, make_float4(w * d.x, w * d.y, w * d.z, w * d.w));
+                const uint32_t idx = entry_index(L, c.gx + (k & 1), c.gy + ((k >> 1) & 1), c.gz + ((k >> 2) & 1));
+                VT::red_keep(tb + (size_t)idx * F, make_float4(w * d.x, w * d.y, w * d.z, w * d.w), keep);
             }
         }
     }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        uint32_t idx = entry_index(L, c0.gx + (k & 1), c0.gy + ((k >> 1) & 1), c0.gz + ((k >> 2) & 1));
-        VT::red(tb + (size_t)idx * F, acc[k]);
-    }
+}
+
+// levels_per_pass trades HBM write/read efficiency of the feature rows (more levels per warp ->
+// longer contiguous runs per row) against L2 residency of the table (fewer levels in flight ->
+// one 128 MiB hashed level is the working set).  Measured on B200, 2^22 random points, default
+// table (profiles/r01_hashgrid_mapping_sweep.md): 1 level/pass is best for a single evaluation,
+// 2 levels/pass for the 7-evaluation tap kernel whose traffic is dominated by feature rows.
+Mapping make_mapping(const na_hashgrid_desc* desc, uint32_t levels, uint32_t n_taps) {
+    Mapping m;
+    m.lanes_per_level = desc->n_features >= 4 ? desc->n_features / 4 : 1;
+    const int max_levels_per_warp = 32 / m.lanes_per_level;
+    int cap = n_taps > 1 ? 2 : 1;
+    if (const char* e = getenv("NA_HG_GROUP")) cap = atoi(e);  // developer knob for the sweep above
+    if (cap > max_levels_per_warp) cap = max_levels_per_warp;
+    int lp = 1;  // levels per pass: power of two so that points-per-warp divides the warp
+    while (lp < (int)levels && lp < cap) lp *= 2;
+    m.levels_per_pass = lp;
+    m.points_per_warp = 32 / (lp * m.lanes_per_level);
+    m.passes = ((int)levels + lp - 1) / lp;
+    m.points_per_cta = 8 * m.points_per_warp * (getenv("NA_HG_ITERS") ? atoi(getenv("NA_HG_ITERS")) : 16);
+    return m;
 }
 
 int validate(const na_hashgrid_desc* desc, const void* a, const void* b, int64_t n_points, uint32_t active_levels) {
@@ -300,15 +434,16 @@ template <int F>
 int launch_fwd(const na_hashgrid_desc* desc, const float* table, const float* x, int64_t n_points, na_unit_map map,
                uint32_t active_levels, const TapParams& tp, float* out, int64_t out_stride, int64_t out_tap_stride,
                cudaStream_t stream) {
-    const int64_t blocks = (n_points + Shape<F>::PTS - 1) / Shape<F>::PTS;
+    const Mapping m = make_mapping(desc, desc->n_levels, tp.n);
+    const int64_t blocks = (n_points + m.points_per_cta - 1) / m.points_per_cta;
     NA_REQUIRE(blocks <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
-    dim3 grid((unsigned)blocks, desc->n_levels);
+    dim3 grid((unsigned)blocks, m.passes);
     if (vec_aligned(out, out_stride, out_tap_stride, F))
         hashgrid_taps_fwd_kernel<F, true><<<grid, kThreads, 0, stream>>>(*desc, table, x, n_points, map, active_levels,
-                                                                         tp, out, out_stride, out_tap_stride);
+                                                                         tp, out, out_stride, out_tap_stride, m);
     else
         hashgrid_taps_fwd_kernel<F, false><<<grid, kThreads, 0, stream>>>(
-            *desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride);
+            *desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride, m);
     NA_CHECK_LAUNCH("hashgrid_taps_fwd_kernel");
     return NA_OK;
 }
@@ -317,15 +452,16 @@ template <int F>
 int launch_bwd(const na_hashgrid_desc* desc, const float* x, int64_t n_points, na_unit_map map,
                uint32_t active_levels, const TapParams& tp, const float* dout, int64_t dout_stride,
                int64_t dout_tap_stride, float* dtable, cudaStream_t stream) {
-    const int64_t blocks = (n_points + Shape<F>::PTS - 1) / Shape<F>::PTS;
+    const Mapping m = make_mapping(desc, active_levels, tp.n);
+    const int64_t blocks = (n_points + m.points_per_cta - 1) / m.points_per_cta;
     NA_REQUIRE(blocks <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
-    dim3 grid((unsigned)blocks, active_levels);
+    dim3 grid((unsigned)blocks, m.passes);
     if (vec_aligned(dout, dout_stride, dout_tap_stride, F))
         hashgrid_taps_bwd_kernel<F, true><<<grid, kThreads, 0, stream>>>(*desc, x, n_points, map, active_levels, tp,
-                                                                         dout, dout_stride, dout_tap_stride, dtable);
+                                                                         dout, dout_stride, dout_tap_stride, dtable, m);
     else
         hashgrid_taps_bwd_kernel<F, false><<<grid, kThreads, 0, stream>>>(*desc, x, n_points, map, active_levels, tp,
-                                                                          dout, dout_stride, dout_tap_stride, dtable);
+                                                                          dout, dout_stride, dout_tap_stride, dtable, m);
     NA_CHECK_LAUNCH("hashgrid_taps_bwd_kernel");
     return NA_OK;
 }

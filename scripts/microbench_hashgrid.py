@@ -20,7 +20,9 @@ e = float(np.float32(1.0 / 8192))
 six = ((0, 0, 0), (e, 0, 0), (-e, 0, 0), (0, e, 0), (0, -e, 0), (0, 0, e), (0, 0, -e))
 
 
-def timeit(fn, iters=5, warm=2):
+ITERS=int(os.environ.get('NA_MB_ITERS','5')); WARM=int(os.environ.get('NA_MB_WARM','2'))
+def timeit(fn, iters=None, warm=None):
+    iters = ITERS if iters is None else iters; warm = WARM if warm is None else warm
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
