@@ -102,6 +102,73 @@ int na_hashgrid_taps_bwd(const na_hashgrid_desc* desc, const float* x, int64_t n
                          const float* dout, int64_t dout_stride, int64_t dout_tap_stride,
                          float* dtable, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * NeuS volume rendering and hierarchical resampling (one warp per ray).
+ * All tensors fp32 contiguous, [n_rays, n_samples(, k)].  `dist_far` is [n_rays] or NULL (= 1e10,
+ * the reference's default).  `s_var` is a DEVICE scalar (the learnable log inverse std-dev).
+ * ---------------------------------------------------------------------------------------- */
+
+/* weights[i] = alphas[i] * prod_{j<i}(1 - alphas[j]).
+ * Replaces: render.alpha_compositing_weights, projects/nerf/utils/render.py:87-99. */
+int na_alpha_weights_fwd(const float* alphas, int64_t n_rays, int n_samples, float* weights, void* stream);
+/* Adjoint by a reverse affine scan (no division by 1-alpha). */
+int na_alpha_weights_bwd(const float* alphas, const float* d_weights, int64_t n_rays, int n_samples,
+                         float* d_alphas, void* stream);
+
+/* out[r,c] = sum_i q[r,i,c] * w[r,i].  Replaces: render.composite, render.py:102-112. */
+int na_composite_fwd(const float* q, const float* w, int64_t n_rays, int n_samples, int k, float* out,
+                     void* stream);
+/* d_q and/or d_w may be NULL when not needed. */
+int na_composite_bwd(const float* q, const float* w, const float* d_out, int64_t n_rays, int n_samples, int k,
+                     float* d_q, float* d_w, void* stream);
+
+/* alpha = 1 - exp(-density * interval).  Replaces: render.volume_rendering_alphas_dist, render.py:68-84. */
+int na_density_alphas_fwd(const float* dens, const float* dists, const float* dist_far, int64_t n_rays,
+                          int n_samples, float* alphas, void* stream);
+int na_density_alphas_bwd(const float* dens, const float* dists, const float* dist_far, const float* d_alphas,
+                          int64_t n_rays, int n_samples, float* d_dens, void* stream);
+
+/* NeuS opacity from SDF value + SDF gradient along the ray; anneal_ratio = min(progress/anneal_end, 1).
+ * Replaces: Model.compute_neus_alphas + _get_iter_cos, projects/neuralangelo/model.py:275-298. */
+int na_neus_alphas_fwd(const float* sdf, const float* grad, const float* dists, const float* ray_unit,
+                       const float* dist_far, const float* s_var, float anneal_ratio, int64_t n_rays,
+                       int n_samples, float* alphas, void* stream);
+/* d_s_var (device scalar) is accumulated atomically; d_sdf [R,N], d_grad [R,N,3] are overwritten. */
+int na_neus_alphas_bwd(const float* sdf, const float* grad, const float* dists, const float* ray_unit,
+                       const float* dist_far, const float* s_var, float anneal_ratio, const float* d_alphas,
+                       int64_t n_rays, int n_samples, float* d_sdf, float* d_grad, float* d_s_var, void* stream);
+
+/* Inverse-CDF sampling: bins [R,n_bins], weights [R,n_bins-1], unif [n_fine] (device; the u values,
+ * normally the midpoints of linspace(0,1,n_fine+1)) -> out [R,n_fine].  2 <= n_bins <= 1024.
+ * Replaces: nerf_util.sample_dists_from_pdf, projects/nerf/utils/nerf_util.py:41-68. */
+int na_sample_pdf(const float* bins, const float* weights, const float* unif, int64_t n_rays, int n_bins,
+                  int n_fine, float* out, void* stream);
+
+/* NeuS hierarchical up-sampling: section opacities from consecutive SDF samples at sharpness inv_s,
+ * compositing weights, inverse-CDF sampling.  2 <= n_samples <= 768.
+ * Replaces: Model.sample_dists_hierarchical, model.py:250-267. */
+int na_neus_upsample(const float* dists, const float* sdfs, const float* unif, float inv_s, int64_t n_rays,
+                     int n_samples, int n_fine, float* dists_fine, void* stream);
+
+/* Merge two per-ray sorted rows (and optionally the SDF values riding along).
+ * Replaces: torch.cat + sort + gather at model.py:241-247. */
+int na_merge_sorted(const float* dists, const float* sdfs, const float* dists_fine, const float* sdfs_fine,
+                    int64_t n_rays, int n_samples, int n_fine, float* dists_out, float* sdfs_out, void* stream);
+
+/* Fused renderer: object NeuS alphas ++ background density alphas -> compositing weights -> RGB.
+ * rgb [R,3]; weights [R,n_obj+n_bg] and opacity [R] optional (NULL).  n_bg may be 0 (no background).
+ * n_obj + n_bg <= 512.  Replaces: model.py:132-141 with the alphas of :168-169 and :198. */
+int na_neus_render_fwd(const float* sdf, const float* grad, const float* dists_obj, const float* ray_unit,
+                       const float* dist_far, const float* s_var, float anneal_ratio, const float* rgb_obj,
+                       int n_obj, const float* dens_bg, const float* dists_bg, const float* rgb_bg, int n_bg,
+                       int64_t n_rays, float* rgb, float* weights, float* opacity, void* stream);
+/* d_weights optional (NULL).  Outputs overwritten except d_s_var (atomic accumulate). */
+int na_neus_render_bwd(const float* sdf, const float* grad, const float* dists_obj, const float* ray_unit,
+                       const float* dist_far, const float* s_var, float anneal_ratio, const float* rgb_obj,
+                       int n_obj, const float* dens_bg, const float* dists_bg, const float* rgb_bg, int n_bg,
+                       int64_t n_rays, const float* d_rgb, const float* d_weights, float* d_sdf, float* d_grad,
+                       float* d_s_var, float* d_rgb_obj, float* d_dens_bg, float* d_rgb_bg, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

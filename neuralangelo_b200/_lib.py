@@ -54,6 +54,21 @@ def _declare(lib):
         "na_hashgrid_bwd": (ctypes.c_int, [descp, vp, i64, UnitMap, u32, vp, i64, vp, vp]),
         "na_hashgrid_taps_fwd": (ctypes.c_int, [descp, vp, vp, i64, UnitMap, u32, c_f32p, u32, vp, i64, i64, vp]),
         "na_hashgrid_taps_bwd": (ctypes.c_int, [descp, vp, i64, UnitMap, u32, c_f32p, u32, vp, i64, i64, vp, vp]),
+        "na_alpha_weights_fwd": (ctypes.c_int, [vp, i64, ctypes.c_int, vp, vp]),
+        "na_alpha_weights_bwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, vp, vp]),
+        "na_composite_fwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp]),
+        "na_composite_bwd": (ctypes.c_int, [vp, vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp, vp]),
+        "na_density_alphas_fwd": (ctypes.c_int, [vp, vp, vp, i64, ctypes.c_int, vp, vp]),
+        "na_density_alphas_bwd": (ctypes.c_int, [vp, vp, vp, vp, i64, ctypes.c_int, vp, vp]),
+        "na_neus_alphas_fwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, f32, i64, ctypes.c_int, vp, vp]),
+        "na_neus_alphas_bwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, f32, vp, i64, ctypes.c_int, vp, vp, vp, vp]),
+        "na_sample_pdf": (ctypes.c_int, [vp, vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp]),
+        "na_neus_upsample": (ctypes.c_int, [vp, vp, vp, f32, i64, ctypes.c_int, ctypes.c_int, vp, vp]),
+        "na_merge_sorted": (ctypes.c_int, [vp, vp, vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp, vp]),
+        "na_neus_render_fwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, f32, vp, ctypes.c_int, vp, vp, vp, ctypes.c_int,
+                                              i64, vp, vp, vp, vp]),
+        "na_neus_render_bwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, f32, vp, ctypes.c_int, vp, vp, vp, ctypes.c_int,
+                                              i64, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -92,7 +107,16 @@ def current_stream():
 
 
 def ptr(t):
-    return ctypes.c_void_p(t.data_ptr())
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def f32c(t):
+    """fp32 contiguous view/copy of a tensor (kernels take dense fp32 rows)."""
+    if t is None:
+        return None
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
 
 
 def require_cuda(*tensors):
