@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200-native Neuralangelo hot path.
+
+Default workload = BASELINE.json configs[1]: hash-grid encode forward + backward microbenchmark,
+16 levels x 8 features, 2^22-entry hashmap (1.46 GB fp32 table), 2^22 points uniform in the unit
+ball mapped to [0.25,0.75]^3, centre + 6 finite-difference taps (eps = 1/2048 world = 1/8192 unit),
+dOut ~ N(0,1).  One "step" = zero the table gradient, encode 7 x 2^22 rows, scatter 7 x 2^22 rows.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload encode]
+
+Prints ONE JSON line (rank 0).  `value` is whole-job algorithmic GB/s with inputs resident in HBM;
+`e2e` is the same metric through the public API with the step's points arriving from pinned HOST
+memory and a device->host read of the step's result inside the timed region.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GROWTH = float(np.exp((np.log(2048) - np.log(32)) / 15))  # modules.py:38-41 for min_logres 5, max_logres 11
+HG_CFG = (16, 8, 22, 32, GROWTH)
+N_POINTS = 1 << 22
+EPS_WORLD = 1.0 / 2048
+ROW_BYTES = 12 + 128 * 4  # one evaluation: xyz in + one 128-float feature row
+
+
+def six_taps(eps):
+    e = float(np.float32(eps))
+    return ((0, 0, 0), (e, 0, 0), (-e, 0, 0), (0, e, 0), (0, -e, 0), (0, 0, e), (0, 0, -e))
+
+
+def unit_ball_points(n, seed, device):
+    """Uniform in the unit ball (radius 1, world coordinates; the [-2,2] volume maps it to [0.25,0.75]^3)."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    p = torch.randn(n, 3, device=device, generator=g)
+    p = p / p.norm(dim=-1, keepdim=True) * torch.rand(n, 1, device=device, generator=g) ** (1.0 / 3.0)
+    return p.contiguous()
+
+
+def algorithmic_bytes(n_points, n_taps, table_bytes):
+    fwd = n_points * n_taps * ROW_BYTES + table_bytes
+    bwd = n_points * n_taps * ROW_BYTES + 2 * table_bytes
+    return fwd, bwd
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            return json.load(fh), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])), mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the CPU restatement of the tcnn hash grid on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_encode_sample(n_sample, threads):
+    """Runs fwd+bwd of the same workload on `n_sample` points on the CPU (oracle port; tcnn itself is
+    CUDA-only and not installable here).  Returns (seconds, equivalent GB/s of the full-size metric)."""
+    from oracle import hashgrid_ref as hr  # CPU baseline leg: the one place bench.py executes oracle/
+    torch.set_num_threads(threads)
+    tbl = hr.level_table(*HG_CFG)
+    table = hr.init_table(tbl)
+    pts = unit_ball_points(n_sample, 0, "cpu")
+    taps = six_taps(EPS_WORLD)
+    g = torch.Generator().manual_seed(1)
+    dout = torch.randn(len(taps), n_sample, 128, generator=g)
+    t0 = time.perf_counter()
+    hr.encode_taps(tbl, table, pts, -2.0, 2.0, taps)
+    for t, off in enumerate(taps):
+        p = pts + torch.tensor(off, dtype=torch.float32)
+        hr.encode_backward(tbl, hr.unit_map(p, -2.0, 2.0), dout[t], dtype=torch.float32)
+    dt = time.perf_counter() - t0
+    fwd, bwd = algorithmic_bytes(N_POINTS, len(taps), table.numel() * 4)
+    # the full-size metric scaled by the fraction of points processed (table term scaled alike)
+    gbps = (fwd + bwd) * (n_sample / N_POINTS) / dt / 1e9
+    return dt, gbps
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    n_sample = 1 << 16
+    times, vals = [], []
+    for i in range(args.warmup + args.steps):
+        dt, gbps = cpu_encode_sample(n_sample, threads)
+        if i >= args.warmup:
+            times.append(dt), vals.append(gbps)
+    value = float(np.mean(vals))
+    line = {
+        "impl": "reference", "metric": "hashgrid_encode_fwd_bwd_algorithmic_GBps", "value": value, "unit": "GB/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean(times)) * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(),
+        "cpu_baseline": {"value": value, "unit": "GB/s", "cores": threads, "kind": "port",
+                         "sample": f"{n_sample} of {N_POINTS} points x 7 taps fwd+bwd per step, full 1.46 GB table; "
+                                   "GB/s = full-size algorithmic bytes x (sample/full) / seconds"},
+        "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config():
+    return {"workload": "BASELINE.json configs[1]: hash-grid encode fwd+bwd, 16 levels x 8 features, 2^22-entry "
+                        "hashmap, 2^22 points/GPU, centre + 6 taps (eps 1/2048)", "points_per_gpu": N_POINTS,
+            "taps": 7, "table_bytes": 45724048 * 8 * 4, "l2_policy": "inputs_exceed_l2 (30 GB of rows + 1.46 GB "
+            "table per step vs 126 MB L2)", "parallelism": "points sharded across ranks, no data-path collective"}
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def run_ours(args, rank, local_rank, world):
+    from neuralangelo_b200 import _lib, build, hashgrid
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    build.build(verbose=False)
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    desc = hashgrid.make_desc(*HG_CFG)
+    taps = six_taps(EPS_WORLD)
+    um = _lib.UnitMap(-2.0, 0.25)
+    g = torch.Generator(device=dev).manual_seed(1337)
+    table = (torch.rand(desc.total_entries * 8, device=dev, generator=g) * 2 - 1) * 1e-4
+    pts = unit_ball_points(N_POINTS, rank, dev)
+    pts_host = pts.cpu().pin_memory()
+    g1 = torch.Generator(device=dev).manual_seed(1 + rank)
+    dout = torch.randn(len(taps), N_POINTS, 128, device=dev, generator=g1)
+    out = torch.empty(len(taps), N_POINTS, 128, device=dev)
+    dtable = torch.zeros_like(table)
+    pts_dev = torch.empty_like(pts)
+    result_host = torch.empty(129, dtype=torch.float32).pin_memory()
+    fwd_bytes, bwd_bytes = algorithmic_bytes(N_POINTS, len(taps), table.numel() * 4)
+    launches = [0]
+
+    def step(x, ev=None):
+        dtable.zero_()
+        if ev:
+            ev[0].record()
+        hashgrid.encode_taps(desc, table, x, um, 16, taps, out=out)
+        if ev:
+            ev[1].record()
+        hashgrid.scatter_taps(desc, x, um, 16, taps, dout, dtable)
+        if ev:
+            ev[2].record()
+        launches[0] += 2
+
+    def step_e2e():
+        pts_dev.copy_(pts_host, non_blocking=True)
+        step(pts_dev)
+        res = torch.cat([out[0, 0], dtable[:262144].sum().reshape(1)])
+        result_host.copy_(res, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step(pts)
+    barrier()
+    launches[0] = 0
+    kernel_events = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        barrier()
+        start.record()
+        for k in range(args.steps):
+            step(pts, kernel_events[k])
+        stop.record()
+        barrier()
+    gpu_launches = launches[0]
+    elapsed_ms = start.elapsed_time(stop)
+    fwd_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in kernel_events]))
+    bwd_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in kernel_events]))
+
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+
+    if world > 1:
+        t = torch.tensor([elapsed_ms, e2e_ms], device=dev, dtype=torch.float64)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        elapsed_ms, e2e_ms = t.tolist()
+    if rank != 0:
+        return
+    ms_per_step = elapsed_ms / args.steps
+    step_bytes = (fwd_bytes + bwd_bytes) * world
+    value = step_bytes / (ms_per_step * 1e-3) / 1e9
+    e2e_value = step_bytes / (e2e_ms / args.steps * 1e-3) / 1e9
+    peaks, peak_kind = measured_peaks()
+    dominant = ("hashgrid_taps_bwd_kernel", bwd_bytes, bwd_ms) if bwd_ms >= fwd_ms else \
+        ("hashgrid_taps_fwd_kernel", fwd_bytes, fwd_ms)
+    achieved = dominant[1] / (dominant[2] * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as fh:
+            traffic = json.load(fh).get(dominant[0])
+    line = {
+        "metric": "hashgrid_encode_fwd_bwd_algorithmic_GBps", "value": value, "unit": "GB/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(),
+        "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": N_POINTS * 12,
+                "d2h_bytes_per_step": 129 * 4, "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": gpu_launches,
+        "clocks": clocks.summary(),
+        "roofline": {"bound": "hbm", "kernel": dominant[0], "achieved": achieved, "peak": peaks["hbm_gbs"],
+                     "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_kind,
+                     "kernel_ms": dominant[2], "algorithmic_bytes": dominant[1],
+                     "other_kernels": {"hashgrid_taps_fwd_kernel": {"ms": fwd_ms, "GBps": fwd_bytes / fwd_ms / 1e6},
+                                       "hashgrid_taps_bwd_kernel": {"ms": bwd_ms, "GBps": bwd_bytes / bwd_ms / 1e6}}},
+    }
+    if not args.no_cpu_baseline and world == 1:
+        threads = os.cpu_count() or 1
+        n_sample = 1 << 17
+        dt, gbps = cpu_encode_sample(n_sample, threads)
+        line["cpu_baseline"] = {"value": gbps, "unit": "GB/s", "cores": threads, "kind": "port",
+                                "sample": f"{n_sample} of {N_POINTS} points x 7 taps fwd+bwd once ({dt:.1f} s), full "
+                                          "1.46 GB table; GB/s = full-size algorithmic bytes x (sample/full) / seconds"}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="encode", choices=["encode"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", 0))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_ours(args, rank, local_rank, world)
+    finally:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
