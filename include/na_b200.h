@@ -169,6 +169,26 @@ int na_neus_render_bwd(const float* sdf, const float* grad, const float* dists_o
                        int64_t n_rays, const float* d_rgb, const float* d_weights, float* d_sdf, float* d_grad,
                        float* d_s_var, float* d_rgb_obj, float* d_dens_bg, float* d_rgb_bg, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Marching cubes on a device-resident fp32 volume [nx,ny,nz] (C order, x slowest), shared
+ * vertices, output identical -- values AND ordering -- to the serial PyMCubes algorithm.
+ * Replaces: mcubes.marching_cubes(sdf, 0.) at projects/neuralangelo/utils/mesh.py:121 and the
+ * `V * intv + xyz[0,0,0]` that follows it (:123).
+ * Two phases because the output size is data dependent:
+ *   na_mc_count  classifies the cells and scans; writes counts[0] = #vertices, counts[1] = #triangles
+ *                (DEVICE uint32[2]); the caller reads them back and allocates;
+ *   na_mc_emit   writes vertices (float64 [nV,3] = index-space position * scale + origin) and
+ *                triangles (int32 [nF,3]); entries beyond the given capacities are dropped.
+ * `scratch` is caller-owned device memory of na_mc_scratch_bytes() bytes, 256-byte aligned, and
+ * must be left untouched between the two calls.
+ * ---------------------------------------------------------------------------------------- */
+int64_t na_mc_scratch_bytes(int nx, int ny, int nz);
+int na_mc_count(const float* volume, int nx, int ny, int nz, double iso, void* scratch, int64_t scratch_size,
+                uint32_t* counts, void* stream);
+int na_mc_emit(const float* volume, int nx, int ny, int nz, double iso, void* scratch, int64_t scratch_size,
+               double scale, const double* origin /* host [3] or NULL */, double* verts, int64_t cap_verts,
+               int32_t* faces, int64_t cap_faces, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -69,6 +69,10 @@ def _declare(lib):
                                               i64, vp, vp, vp, vp]),
         "na_neus_render_bwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, f32, vp, ctypes.c_int, vp, vp, vp, ctypes.c_int,
                                               i64, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+        "na_mc_scratch_bytes": (ctypes.c_int64, [ctypes.c_int, ctypes.c_int, ctypes.c_int]),
+        "na_mc_count": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double, vp, i64, vp, vp]),
+        "na_mc_emit": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double, vp, i64,
+                                      ctypes.c_double, ctypes.POINTER(ctypes.c_double), vp, i64, vp, i64, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -1,0 +1,280 @@
+"""Drop-in for `projects/neuralangelo/utils/mesh.py`: blocked isosurface extraction with the marching
+cubes running on the GPU (csrc/mcubes.cu) and no host round trip per block.
+
+Same call surface as the reference:
+    extract_mesh(sdf_func, bounds, intv, block_res=64, texture_func=None, filter_lcc=False)
+        -> mesh object on rank 0 (attributes .vertices [nV,3] float64, .faces [nF,3] int64,
+           .visual.vertex_colors, .export(path), .update_faces(mask), .nondegenerate_faces()), None elsewhere
+    LatticeGrid(bounds, intv, block_res)      -- same block geometry / indexing (mesh.py:68-100)
+    marching_cubes(sdf, xyz, intv, texture_func, filter_lcc)
+plus `mc(volume, isovalue)` = the `mcubes.marching_cubes` replacement on device tensors.
+trimesh (reference requirements.txt:34) is not available; `Mesh` below is the minimal container the
+extraction path needs.  Deviation from the reference, on purpose: when the block count is not a
+multiple of the world size, `DistributedSampler` pads by repeating the first blocks and the reference
+concatenates those duplicates into the output (mesh.py:104-105,43-46); here every block is meshed once.
+"""
+import ctypes
+import types
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from ._lib import ptr
+
+_L = _lib.lib
+
+
+def mc(volume, isovalue=0.0, scale=1.0, origin=None):
+    """`mcubes.marching_cubes(volume, isovalue)` on a CUDA float32 tensor [X,Y,Z].
+    Returns (vertices float64 [nV,3], triangles int64 [nF,3]) on the same device; vertex and face
+    order are those of the serial algorithm.  vertices = index position * scale + origin (mesh.py:123)."""
+    _lib.require_cuda(volume)
+    vol = _lib.f32c(volume)
+    nx, ny, nz = vol.shape
+    dev = vol.device
+    nbytes = _L().na_mc_scratch_bytes(nx, ny, nz)
+    scratch = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
+    base = (scratch.data_ptr() + 255) // 256 * 256
+    sptr = ctypes.c_void_p(base)
+    counts = torch.empty(2, dtype=torch.int32, device=dev)
+    stream = _lib.current_stream()
+    _lib.check(_L().na_mc_count(ptr(vol), nx, ny, nz, float(isovalue), sptr, nbytes, ptr(counts), stream), "na_mc_count")
+    n_v, n_f = (int(c) for c in counts.cpu())
+    verts = torch.empty(n_v, 3, dtype=torch.float64, device=dev)
+    faces = torch.empty(n_f, 3, dtype=torch.int32, device=dev)
+    if n_v or n_f:
+        org = None
+        if origin is not None:
+            org = (ctypes.c_double * 3)(*[float(o) for o in origin])
+        _lib.check(_L().na_mc_emit(ptr(vol), nx, ny, nz, float(isovalue), sptr, nbytes, float(scale), org,
+                                   ptr(verts) if n_v else None, n_v, ptr(faces) if n_f else None, n_f, stream),
+                   "na_mc_emit")
+    return verts, faces.long()
+
+
+class Mesh:
+    """Vertices / faces / per-vertex colours on the host (numpy), the subset of trimesh.Trimesh used by
+    mesh.py:43-47,126-158 and scripts/extract_mesh.py:92-101."""
+
+    def __init__(self, vertices=None, faces=None, vertex_colors=None):
+        self.vertices = np.zeros((0, 3), dtype=np.float64) if vertices is None else np.asarray(vertices, dtype=np.float64)
+        self.faces = np.zeros((0, 3), dtype=np.int64) if faces is None else np.asarray(faces, dtype=np.int64)
+        if vertex_colors is None:
+            vertex_colors = np.full((len(self.vertices), 4), 255, dtype=np.uint8)
+            vertex_colors[:, :3] = 102  # trimesh's default grey
+        vertex_colors = np.asarray(vertex_colors, dtype=np.uint8)
+        if vertex_colors.shape[-1] == 3:
+            vertex_colors = np.concatenate([vertex_colors, np.full((len(vertex_colors), 1), 255, np.uint8)], axis=-1)
+        self.visual = types.SimpleNamespace(vertex_colors=vertex_colors)
+
+    @property
+    def area_faces(self):
+        v = self.vertices[self.faces]
+        return 0.5 * np.linalg.norm(np.cross(v[:, 1] - v[:, 0], v[:, 2] - v[:, 0]), axis=-1)
+
+    @property
+    def area(self):
+        return float(self.area_faces.sum())
+
+    def nondegenerate_faces(self):
+        f = self.faces
+        return (f[:, 0] != f[:, 1]) & (f[:, 1] != f[:, 2]) & (f[:, 0] != f[:, 2])
+
+    def update_faces(self, mask):
+        self.faces = self.faces[np.asarray(mask)]
+
+    def split(self, only_watertight=False):
+        """Connected components (by shared vertices) as separate meshes."""
+        labels = _face_components(self.faces, len(self.vertices))
+        out = []
+        for lab in np.unique(labels):
+            fm = labels == lab
+            used = np.unique(self.faces[fm])
+            remap = np.full(len(self.vertices), -1, dtype=np.int64)
+            remap[used] = np.arange(len(used))
+            out.append(Mesh(self.vertices[used], remap[self.faces[fm]], self.visual.vertex_colors[used]))
+        return out
+
+    def export(self, path):
+        """Binary little-endian PLY with per-vertex colours (what trimesh's exporter writes for .ply)."""
+        v = self.vertices.astype("<f4")
+        c = self.visual.vertex_colors.astype(np.uint8)
+        header = ("ply\nformat binary_little_endian 1.0\n"
+                  f"element vertex {len(v)}\nproperty float x\nproperty float y\nproperty float z\n"
+                  "property uchar red\nproperty uchar green\nproperty uchar blue\nproperty uchar alpha\n"
+                  f"element face {len(self.faces)}\nproperty list uchar int vertex_indices\nend_header\n")
+        vrec = np.empty(len(v), dtype=[("p", "<f4", 3), ("c", "u1", 4)])
+        vrec["p"], vrec["c"] = v, c
+        frec = np.empty(len(self.faces), dtype=[("n", "u1"), ("i", "<i4", 3)])
+        frec["n"], frec["i"] = 3, self.faces.astype("<i4")
+        with open(path, "wb") as fh:
+            fh.write(header.encode("ascii"))
+            fh.write(vrec.tobytes())
+            fh.write(frec.tobytes())
+
+
+def _face_components(faces, n_vertices):
+    """Union-find over vertices; returns the component label of each face."""
+    parent = np.arange(n_vertices, dtype=np.int64)
+
+    def find(x):
+        while True:
+            p = parent[x]
+            gp = parent[p]
+            if np.array_equal(p, gp):
+                return p
+            parent[x] = gp
+            x = gp
+
+    if len(faces) == 0:
+        return np.zeros(0, dtype=np.int64)
+    for a, b in ((0, 1), (1, 2)):
+        while True:
+            ra, rb = find(faces[:, a]), find(faces[:, b])
+            diff = ra != rb
+            if not diff.any():
+                break
+            lo, hi = np.minimum(ra[diff], rb[diff]), np.maximum(ra[diff], rb[diff])
+            parent[hi] = lo
+    return find(faces[:, 0])
+
+
+def concatenate(meshes):
+    """trimesh.util.concatenate: stack vertices, offset face indices (no welding across blocks, mesh.py:46)."""
+    if not meshes:
+        return Mesh()
+    offs = np.cumsum([0] + [len(m.vertices) for m in meshes[:-1]])
+    return Mesh(np.concatenate([m.vertices for m in meshes]),
+                np.concatenate([m.faces + o for m, o in zip(meshes, offs)]),
+                np.concatenate([m.visual.vertex_colors for m in meshes]))
+
+
+class LatticeGrid(torch.utils.data.Dataset):
+    """Blocked lattice over `bounds` with step `intv` (mesh.py:68-100): same grids (torch.arange on the CPU,
+    float32), same block count / index order / 1-slice overlap, truncated at the far faces."""
+
+    def __init__(self, bounds, intv, block_res=64):
+        super().__init__()
+        self.block_res = block_res
+        ((x_min, x_max), (y_min, y_max), (z_min, z_max)) = bounds
+        self.x_grid = torch.arange(x_min, x_max, intv)
+        self.y_grid = torch.arange(y_min, y_max, intv)
+        self.z_grid = torch.arange(z_min, z_max, intv)
+        res_x, res_y, res_z = len(self.x_grid), len(self.y_grid), len(self.z_grid)
+        self.resolution = (res_x, res_y, res_z)
+        self.num_blocks_x = int(np.ceil(res_x / block_res))
+        self.num_blocks_y = int(np.ceil(res_y / block_res))
+        self.num_blocks_z = int(np.ceil(res_z / block_res))
+
+    def block_axes(self, idx):
+        bx = idx // (self.num_blocks_y * self.num_blocks_z)
+        by = (idx // self.num_blocks_z) % self.num_blocks_y
+        bz = idx % self.num_blocks_z
+        r = self.block_res
+        return (self.x_grid[bx * r:bx * r + r + 1], self.y_grid[by * r:by * r + r + 1],
+                self.z_grid[bz * r:bz * r + r + 1])
+
+    def __getitem__(self, idx):
+        x, y, z = torch.meshgrid(*self.block_axes(idx), indexing="ij")
+        return dict(idx=idx, xyz=torch.stack([x, y, z], dim=-1))
+
+    def __len__(self):
+        return self.num_blocks_x * self.num_blocks_y * self.num_blocks_z
+
+
+def _world():
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def filter_points_outside_bounding_sphere(verts, faces, colors=None):
+    """mesh.py:136-148 on device tensors: keep vertices with |v| < 1 and the faces made only of kept vertices."""
+    mask = verts.norm(dim=-1) < 1.0
+    if not bool(mask.any()):
+        return verts[:0], faces[:0], (colors[:0] if colors is not None else None)
+    remap = torch.full((len(verts),), -1, dtype=torch.long, device=verts.device)
+    remap[mask] = torch.arange(int(mask.sum()), device=verts.device)
+    fmask = mask[faces[:, 0]] & mask[faces[:, 1]] & mask[faces[:, 2]]
+    return verts[mask], remap[faces[fmask]], (colors[mask] if colors is not None else None)
+
+
+def filter_largest_cc(mesh):
+    """mesh.py:151-158: keep the connected component with the largest surface area."""
+    components = mesh.split(only_watertight=False)
+    areas = np.array([c.area for c in components], dtype=float)
+    if len(areas) > 0 and mesh.vertices.shape[0] > 0:
+        return components[areas.argmax()]
+    return Mesh()
+
+
+def marching_cubes(sdf, xyz, intv, texture_func, filter_lcc):
+    """mesh.py:119-133 for one block.  sdf [X,Y,Z] and xyz [X,Y,Z,3] are CUDA tensors; returns device
+    tensors (V float64, F int64, C uint8|None) -- the host Mesh is only built once, on rank 0."""
+    origin = xyz[0, 0, 0].double().tolist()
+    V, F = mc(sdf, 0.0, scale=float(intv), origin=origin)
+    C = None
+    if V.shape[0] > 0:
+        if texture_func is not None:
+            C = torch.as_tensor(texture_func(V.cpu().numpy()), device=V.device)
+        V, F, C = filter_points_outside_bounding_sphere(V, F, C)
+        if filter_lcc and V.shape[0] > 0:
+            m = filter_largest_cc(Mesh(V.cpu().numpy(), F.cpu().numpy(), None if C is None else C.cpu().numpy()))
+            V = torch.as_tensor(m.vertices, device=sdf.device)
+            F = torch.as_tensor(m.faces, device=sdf.device)
+            C = None if C is None else torch.as_tensor(m.visual.vertex_colors[:, :3], device=sdf.device)
+    return V, F, C
+
+
+def _gather_to_rank0(t, rank, world, device):
+    """Variable-length gather of a [n, k] tensor to rank 0 (replaces the pickled all_gather_object, mesh.py:38-40)."""
+    n = torch.tensor([t.shape[0]], dtype=torch.long, device=device)
+    sizes = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(sizes, n)
+    sizes = [int(s) for s in sizes]
+    cap = max(max(sizes), 1)
+    pad = torch.zeros(cap, *t.shape[1:], dtype=t.dtype, device=device)
+    pad[:t.shape[0]] = t
+    out = [torch.zeros_like(pad) for _ in range(world)] if rank == 0 else None
+    dist.gather(pad, out, dst=0)
+    if rank != 0:
+        return None, sizes
+    return [o[:s] for o, s in zip(out, sizes)], sizes
+
+
+@torch.no_grad()
+def extract_mesh(sdf_func, bounds, intv, block_res=64, texture_func=None, filter_lcc=False, device=None):
+    """mesh.py:24-49.  Blocks are dealt round-robin to ranks exactly as DistributedSampler(shuffle=False)
+    does (block idx = rank, rank + W, ...); each block's lattice is built on the device, queried, meshed
+    and filtered there; rank 0 receives the vertex / face buffers and concatenates them."""
+    rank, world = _world()
+    device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+    grid = LatticeGrid(bounds, intv=intv, block_res=block_res)
+    v_parts, f_parts, c_parts, v_total = [], [], [], 0
+    for idx in range(rank, len(grid), world):
+        gx, gy, gz = (g.to(device) for g in grid.block_axes(idx))
+        xyz = torch.stack(torch.meshgrid(gx, gy, gz, indexing="ij"), dim=-1)
+        sdf = sdf_func(xyz)[..., 0]
+        V, F, C = marching_cubes(sdf, xyz, intv, texture_func, filter_lcc)
+        if V.shape[0] > 0:
+            v_parts.append(V)
+            f_parts.append(F + v_total)
+            c_parts.append(C)
+            v_total += V.shape[0]
+    V = torch.cat(v_parts) if v_parts else torch.zeros(0, 3, dtype=torch.float64, device=device)
+    F = torch.cat(f_parts) if f_parts else torch.zeros(0, 3, dtype=torch.long, device=device)
+    textured = texture_func is not None
+    C = (torch.cat(c_parts) if c_parts else torch.zeros(0, 3, dtype=torch.uint8, device=device)) if textured else None
+    if world > 1:
+        Vs, v_sizes = _gather_to_rank0(V, rank, world, device)
+        Fs, _ = _gather_to_rank0(F, rank, world, device)
+        Cs = _gather_to_rank0(C, rank, world, device)[0] if textured else None
+        if rank != 0:
+            return None
+        offs = np.cumsum([0] + v_sizes[:-1])
+        V = torch.cat(Vs)
+        F = torch.cat([f + int(o) for f, o in zip(Fs, offs)])
+        C = torch.cat(Cs) if textured else None
+    return Mesh(V.cpu().numpy(), F.cpu().numpy(), None if C is None else C.cpu().numpy())
