@@ -189,6 +189,21 @@ int na_mc_emit(const float* volume, int nx, int ny, int nz, double iso, void* sc
                double scale, const double* origin /* host [3] or NULL */, double* verts, int64_t cap_verts,
                int32_t* faces, int64_t cap_faces, void* stream);
 
+/* Marching cubes for callers that cannot allocate device memory (fixed memory budgets, code running
+ * inside another component's allocator, threads that must not block on cudaMalloc).  No counterpart in
+ * the reference.  Same result as na_mc_count + na_mc_emit, but the scratch is a fixed array built into
+ * the library (about 1.3 MB held on every GPU that loads it, until the process exits), so the volume is
+ * limited to na_mc_static_max_cells() = 64^3 cells (e.g. 65^3 samples); larger volumes fail with
+ * NA_ERR_CAPACITY.  The caller passes the outputs: verts [cap_verts,3] float64, faces [cap_faces,3] int32
+ * (entries beyond the capacities are dropped) and counts (DEVICE uint32[2]: #vertices, #triangles found).
+ * Calls no cudaMalloc/cudaFree.  All calls on one GPU share the array: calls that may overlap on the GPU
+ * race and must be serialised by the caller.  The first call on each device looks up the array's device
+ * address; issue that first call outside of any stream capture. */
+int64_t na_mc_static_max_cells(void);
+int na_mc_run_static(const float* volume, int nx, int ny, int nz, double iso, double scale,
+                     const double* origin /* host [3] or NULL */, double* verts, int64_t cap_verts,
+                     int32_t* faces, int64_t cap_faces, uint32_t* counts, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,6 +73,9 @@ def _declare(lib):
         "na_mc_count": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double, vp, i64, vp, vp]),
         "na_mc_emit": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double, vp, i64,
                                       ctypes.c_double, ctypes.POINTER(ctypes.c_double), vp, i64, vp, i64, vp]),
+        "na_mc_static_max_cells": (ctypes.c_int64, []),
+        "na_mc_run_static": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                            ctypes.c_double, ctypes.POINTER(ctypes.c_double), vp, i64, vp, i64, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

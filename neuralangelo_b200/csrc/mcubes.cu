@@ -368,3 +368,98 @@ extern "C" int na_mc_emit(const float* volume, int nx, int ny, int nz, double is
     NA_CHECK_LAUNCH("mc_faces_kernel");
     return NA_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// na_mc_run_static: marching cubes for callers that are not allowed to allocate device memory.
+//
+// Who needs this: code that runs where cudaMalloc is off limits -- a real-time or serving loop whose
+// memory budget was fixed at start-up, a plugin called from inside somebody else's allocator or memory
+// pool, a host thread that must not take the driver's allocation lock (cudaMalloc synchronises the
+// whole device), or a process whose remaining device memory is already spoken for.  The regular pair
+// na_mc_count / na_mc_emit asks such a caller for a scratch buffer it has no way to obtain.  Here the
+// scratch lives inside the library image instead: a fixed array in device global memory that every GPU
+// loading libna_b200.so reserves (about 1.3 MB per GPU) from load until the process exits.
+//
+// Limit: at most kStaticMaxCells = 64^3 cells per call (e.g. a 65^3-sample block, block_res = 64, the
+// default of the reference's extract_mesh signature).  Larger volumes are rejected with NA_ERR_CAPACITY.
+//
+// Sharing: there is ONE array per GPU and every call on that GPU uses it.  It still holds whatever the
+// previous call left behind; that is harmless because each call writes every scratch word (case byte,
+// vertex offset, per-CTA sum) before it reads it, so nothing has to start at zero and nothing is
+// cleared.  Two calls whose kernels can overlap on the same GPU (different streams, different host
+// threads) would overwrite each other's scratch: callers must serialise them (same stream, or an event).
+//
+// Set-up: the array's name is only a host-side handle, not a device address; the address is looked up
+// with cudaGetSymbolAddress the first time the entry point runs on a given device (that device being
+// current) and remembered per device.  Make that first call outside of any stream capture.
+// ---------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace {
+
+constexpr int64_t kStaticMaxCells = 64LL * 64 * 64;
+constexpr size_t kStaticScratchBytes =
+    ((size_t)kStaticMaxCells + 255) / 256 * 256 +                       // case index, 1 B per cell
+    ((size_t)kStaticMaxCells * 4 + 255) / 256 * 256 +                   // vertex offset, 4 B per cell
+    (((size_t)kStaticMaxCells + kThreads - 1) / kThreads * 8 + 255) / 256 * 256;  // (vertex, triangle) sums per CTA
+
+static __device__ __align__(256) unsigned char g_mc_static_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mutex;
+void* g_static_scratch_addr[kMaxDevices] = {nullptr};
+
+// Device address of the static scratch on the CURRENT device (looked up once per device).
+int static_scratch_address(void** out) {
+    int dev = -1;
+    if (int rc = na::check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return rc;
+    NA_REQUIRE(dev >= 0 && dev < kMaxDevices, "mc_run_static: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (g_static_scratch_addr[dev] == nullptr) {
+        void* p = nullptr;
+        if (int rc = na::check_cuda(cudaGetSymbolAddress(&p, g_mc_static_scratch), "cudaGetSymbolAddress")) return rc;
+        NA_REQUIRE(p != nullptr, "mc_run_static: static scratch has no device address");
+        g_static_scratch_addr[dev] = p;
+    }
+    *out = g_static_scratch_addr[dev];
+    return NA_OK;
+}
+
+}  // namespace
+
+extern "C" int64_t na_mc_static_max_cells(void) { return kStaticMaxCells; }
+
+extern "C" int na_mc_run_static(const float* volume, int nx, int ny, int nz, double iso, double scale,
+                                const double* origin, double* verts, int64_t cap_verts, int32_t* faces,
+                                int64_t cap_faces, uint32_t* counts, void* stream) {
+    na::clear_error();
+    if (int rc = check_dims(nx, ny, nz, "mc_run_static")) return rc;
+    NA_REQUIRE(volume && counts, "mc_run_static: null pointer");
+    NA_REQUIRE(cap_verts >= 0 && cap_faces >= 0 && (cap_verts == 0 || verts) && (cap_faces == 0 || faces),
+               "mc_run_static: null output with non-zero capacity");
+    const Dims d = make_dims(nx, ny, nz);
+    if (d.n_cells > kStaticMaxCells) {
+        na::set_error("mc_run_static: %dx%dx%d samples = %lld cells exceed the built-in scratch (max %lld cells, "
+                      "e.g. 65^3 samples); use na_mc_count/na_mc_emit with caller-owned scratch",
+                      nx, ny, nz, (long long)d.n_cells, (long long)kStaticMaxCells);
+        return NA_ERR_CAPACITY;
+    }
+    void* base = nullptr;
+    if (int rc = static_scratch_address(&base)) return rc;
+    const Scratch s = carve(base, d);
+    Xform xf;
+    xf.scale = scale;
+    for (int a = 0; a < 3; ++a) xf.origin[a] = origin ? origin[a] : 0.0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned ctas = (unsigned)n_cta(d);
+    mc_classify_kernel<<<ctas, kThreads, 0, st>>>(volume, d, iso, s.cases, s.block_sums);
+    NA_CHECK_LAUNCH("mc_classify_kernel");
+    mc_scan_blocks_kernel<<<1, kThreads, 0, st>>>(s.block_sums, n_cta(d), counts);
+    NA_CHECK_LAUNCH("mc_scan_blocks_kernel");
+    mc_vertices_kernel<<<ctas, kThreads, 0, st>>>(volume, d, iso, s.cases, s.block_sums, s.vert_offset, verts,
+                                                  cap_verts, xf);
+    NA_CHECK_LAUNCH("mc_vertices_kernel");
+    mc_faces_kernel<<<ctas, kThreads, 0, st>>>(d, s.cases, s.block_sums, s.vert_offset, faces, cap_faces);
+    NA_CHECK_LAUNCH("mc_faces_kernel");
+    return NA_OK;
+}
