@@ -1,0 +1,147 @@
+"""Weight-normed skip MLPs of the Neuralangelo path, with the reference's module/parameter names so that
+its checkpoints load unchanged (`linears.{i}.{weight_g,weight_v,bias}`, `linear_sdf.{weight,bias}`).
+
+Mirrors `projects/neuralangelo/utils/mlp.py:18-84` (MLPforNeuralSDF) and
+`projects/nerf/utils/nerf_util.py:158-196` (MLPwithSkipConnection).  The weight-norm reparametrisation
+W = g * v / ||v|| is evaluated once per forward of the whole MLP (the reference's hook recomputes it on
+every `linear(...)` call, >= 7 times per step for the SDF MLP).
+"""
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+
+def get_activation(activ, **kwargs):
+    """projects/neuralangelo/utils/misc.py:92-107 (the activations the path uses)."""
+    if activ in ("relu", "relu_"):
+        return F.relu
+    if activ == "softplus":
+        beta = float(kwargs.get("beta", 1.0))
+        return lambda x: F.softplus(x, beta=beta)
+    if activ == "identity":
+        return lambda x: x
+    if activ in ("sigmoid", "sigmoid_"):
+        return torch.sigmoid
+    if activ in ("silu", "silu_"):
+        return F.silu
+    if activ in ("abs", "abs_"):
+        return torch.abs
+    if activ in ("exp", "exp_"):
+        return torch.exp
+    raise KeyError(activ)
+
+
+class Linear(torch.nn.Module):
+    """nn.Linear, optionally weight-normed with the legacy `weight_g` / `weight_v` parameter names of
+    `torch.nn.utils.weight_norm` (dim=0: one norm per output row)."""
+
+    def __init__(self, k_in, k_out, weight_norm=False):
+        super().__init__()
+        self.in_features, self.out_features, self.weight_norm = k_in, k_out, weight_norm
+        w = torch.empty(k_out, k_in)
+        torch.nn.init.kaiming_uniform_(w, a=np.sqrt(5))
+        bound = 1 / np.sqrt(k_in)
+        self.bias = torch.nn.Parameter(torch.empty(k_out).uniform_(-bound, bound))
+        if weight_norm:
+            self.weight_g = torch.nn.Parameter(w.norm(dim=1, keepdim=True))
+            self.weight_v = torch.nn.Parameter(w)
+        else:
+            self.weight = torch.nn.Parameter(w)
+
+    def set_weight(self, w):
+        """Assign the effective weight (used by the initialisers, which run before weight-norm in the reference)."""
+        with torch.no_grad():
+            if self.weight_norm:
+                self.weight_v.copy_(w)
+                self.weight_g.copy_(w.norm(dim=1, keepdim=True))
+            else:
+                self.weight.copy_(w)
+
+    def effective_weight(self):
+        if not self.weight_norm:
+            return self.weight
+        return self.weight_v * (self.weight_g / self.weight_v.norm(dim=1, keepdim=True))
+
+    def forward(self, x):
+        return F.linear(x, self.effective_weight(), self.bias)
+
+
+class MLPforNeuralSDF(torch.nn.Module):
+    """mlp.py:18-84.  forward(input, with_sdf, with_feat) -> [sdf | None, feat | None]; the SDF head reads the
+    INPUT of the last feature layer (mlp.py:66-67)."""
+
+    def __init__(self, layer_dims, skip_connection=(), activ=None, use_layernorm=False, use_weightnorm=False,
+                 geometric_init=False, out_bias=0., invert=False):
+        super().__init__()
+        if use_layernorm:
+            raise NotImplementedError("layer norm is not used on the Neuralangelo path (base.yaml)")
+        self.skip_connection = list(skip_connection)
+        self.linears = torch.nn.ModuleList()
+        pairs = list(zip(layer_dims[:-1], layer_dims[1:]))
+        for li, (k_in, k_out) in enumerate(pairs):
+            if li in self.skip_connection:
+                k_in += layer_dims[0]
+            lin = Linear(k_in, k_out, weight_norm=use_weightnorm)
+            if geometric_init:  # mlp.py:71-77
+                w = torch.empty(k_out, k_in).normal_(0.0, np.sqrt(2 / k_out))
+                if li == 0:
+                    w[:, 3:] = 0.0
+                if li in self.skip_connection:
+                    w[:, -layer_dims[0]:] = 0.0
+                lin.set_weight(w)
+                torch.nn.init.constant_(lin.bias, 0.0)
+            if li == len(pairs) - 1:
+                torch.nn.init.constant_(lin.bias, 0.0)
+            self.linears.append(lin)
+        self.linear_sdf = Linear(k_in, 1)
+        if geometric_init:  # mlp.py:79-84
+            with torch.no_grad():
+                self.linear_sdf.weight.normal_(mean=np.sqrt(np.pi / k_in), std=0.0001)
+                self.linear_sdf.bias.fill_(-out_bias)
+                if invert:
+                    self.linear_sdf.weight.mul_(-1)
+                    self.linear_sdf.bias.mul_(-1)
+        self.activ = activ or F.relu
+
+    def forward(self, input, with_sdf=True, with_feat=True):
+        feat = input
+        n = len(self.linears)
+        for li, linear in enumerate(self.linears):
+            if li in self.skip_connection:
+                feat = torch.cat([feat, input], dim=-1)
+            last = li == n - 1
+            if last:
+                sdf = self.linear_sdf(feat) if with_sdf else None
+                out_feat = self.activ(linear(feat)) if with_feat else None
+                return [sdf, out_feat]
+            feat = self.activ(linear(feat))
+
+
+class MLPwithSkipConnection(torch.nn.Module):
+    """nerf_util.py:158-196."""
+
+    def __init__(self, layer_dims, skip_connection=(), activ=None, use_layernorm=False, use_weightnorm=False):
+        super().__init__()
+        if use_layernorm:
+            raise NotImplementedError("layer norm is not used on the Neuralangelo path (base.yaml)")
+        self.skip_connection = list(skip_connection)
+        self.linears = torch.nn.ModuleList()
+        pairs = list(zip(layer_dims[:-1], layer_dims[1:]))
+        for li, (k_in, k_out) in enumerate(pairs):
+            if li in self.skip_connection:
+                k_in += layer_dims[0]
+            lin = Linear(k_in, k_out, weight_norm=use_weightnorm)
+            if li == len(pairs) - 1:
+                torch.nn.init.constant_(lin.bias, 0.0)
+            self.linears.append(lin)
+        self.activ = activ or F.relu
+
+    def forward(self, input):
+        feat = input
+        for li, linear in enumerate(self.linears):
+            if li in self.skip_connection:
+                feat = torch.cat([feat, input], dim=-1)
+            feat = linear(feat)
+            if li != len(self.linears) - 1:
+                feat = self.activ(feat)
+        return feat

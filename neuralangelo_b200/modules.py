@@ -1,0 +1,300 @@
+"""Drop-in for `projects/neuralangelo/utils/modules.py`: NeuralSDF, NeuralRGB, BackgroundNeRF with the
+reference's constructor arguments, method names, attributes and state-dict keys.
+
+What changes underneath (reference lines in brackets):
+  * the hash grid is `hashgrid.HashGridEncoding` (csrc/hashgrid.cu) instead of tinycudann [modules.py:50,85];
+    the [0,1] normalisation, the coarse-to-fine mask and the `cat([xyz, enc])` [modules.py:81-94] are folded
+    into the encode call: features land at column 3 of a [N,131] row view, inactive levels are written as zeros;
+  * compute_gradients in numerical mode evaluates the centre + 4/6 taps with ONE encode launch that shares
+    corner rows between taps, followed by one MLP pass over all taps [modules.py:132-175 make 4/6 separate
+    encode + MLP round trips].
+"""
+from functools import partial
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from . import _lib, hashgrid
+from .mlp import MLPforNeuralSDF, MLPwithSkipConnection, get_activation
+from .spherical_harmonics import get_spherical_harmonics
+
+
+def positional_encoding(input, num_freq_bases):
+    """nerf_util.py:134-147: [.., N] -> [.., 2*N*L], per input dim: sin(2^l pi x) for all l, then cos."""
+    freq = 2 ** torch.arange(num_freq_bases, dtype=torch.float32, device=input.device) * np.pi
+    spectrum = input[..., None] * freq
+    enc = torch.stack([spectrum.sin(), spectrum.cos()], dim=-2)
+    return enc.view(*input.shape[:-1], -1)
+
+
+class _EncodeRows(torch.autograd.Function):
+    """[T,N,3+L*F] rows = (x + tap_t) ++ hash-grid features of (x + tap_t); gradient to the table only."""
+
+    @staticmethod
+    def forward(ctx, pts, table, module, unit_map, active_levels, taps):
+        width = module.n_output_dims
+        n, n_taps = pts.shape[0], len(taps)
+        # rows padded to 3+width+1 floats with the pad in FRONT: features start 16 bytes into the row, so the
+        # kernel's 16-byte vector stores apply; the returned view drops the pad column.
+        buf = torch.empty(n_taps, n, width + 4, dtype=torch.float32, device=pts.device)
+        offs = torch.tensor(taps, dtype=torch.float32, device=pts.device)
+        buf[:, :, 1:4] = pts[None, :, :] + offs[:, None, :]
+        hashgrid.encode_taps(module.desc, table, pts, unit_map, active_levels, taps, out=buf[:, :, 4:])
+        ctx.save_for_backward(pts)
+        ctx.module, ctx.args = module, (unit_map, active_levels, taps)
+        return buf[:, :, 1:]
+
+    @staticmethod
+    def backward(ctx, drows):
+        (pts,) = ctx.saved_tensors
+        module = ctx.module
+        unit_map, active_levels, taps = ctx.args
+        if not ctx.needs_input_grad[1]:
+            return None, None, None, None, None, None
+        dtable = module._grad_buffer()
+        hashgrid.scatter_taps(module.desc, pts, unit_map, active_levels, taps, drows[:, :, 3:], dtable)
+        if module.accumulate_grad_in_place:
+            return None, None, None, None, None, None
+        return None, dtable, None, None, None, None
+
+
+class NeuralSDF(torch.nn.Module):
+
+    def __init__(self, cfg_sdf):
+        super().__init__()
+        self.cfg_sdf = cfg_sdf
+        encoding_dim = self.build_encoding(cfg_sdf.encoding)
+        self.build_mlp(cfg_sdf.mlp, input_dim=3 + encoding_dim)
+
+    def build_encoding(self, cfg_encoding):
+        if cfg_encoding.type == "fourier":
+            return 6 * cfg_encoding.levels
+        if cfg_encoding.type != "hashgrid":
+            raise NotImplementedError("Unknown encoding type")
+        # modules.py:36-54
+        l_min, l_max = cfg_encoding.hashgrid.min_logres, cfg_encoding.hashgrid.max_logres
+        r_min, r_max = 2 ** l_min, 2 ** l_max
+        num_levels = cfg_encoding.levels
+        self.growth_rate = np.exp((np.log(r_max) - np.log(r_min)) / (num_levels - 1))
+        config = dict(otype="HashGrid", n_levels=cfg_encoding.levels, n_features_per_level=cfg_encoding.hashgrid.dim,
+                      log2_hashmap_size=cfg_encoding.hashgrid.dict_size,
+                      base_resolution=2 ** cfg_encoding.hashgrid.min_logres, per_level_scale=self.growth_rate)
+        self.tcnn_encoding = hashgrid.Encoding(3, config)
+        self.resolutions = [int(np.floor(r_min * self.growth_rate ** lv).astype(int) + 1) for lv in range(num_levels)]
+        vol_min, vol_max = cfg_encoding.hashgrid.range
+        self._unit_map = _lib.UnitMap(float(vol_min), float(np.float32(1.0) / np.float32(vol_max - vol_min)))
+        self.active_levels = num_levels  # until set_active_levels is called (coarse2fine) -- all levels
+        return cfg_encoding.hashgrid.dim * cfg_encoding.levels
+
+    def build_mlp(self, cfg_mlp, input_dim=3):
+        layer_dims = [input_dim] + [cfg_mlp.hidden_dim] * cfg_mlp.num_layers + [cfg_mlp.hidden_dim]
+        activ = get_activation(cfg_mlp.activ, **cfg_mlp.activ_params)
+        self.mlp = MLPforNeuralSDF(layer_dims, skip_connection=cfg_mlp.skip, activ=activ,
+                                   use_weightnorm=cfg_mlp.weight_norm, geometric_init=cfg_mlp.geometric_init,
+                                   out_bias=cfg_mlp.out_bias, invert=cfg_mlp.inside_out)
+
+    # ------------------------------------------------------------------------------------------
+    def _hashgrid(self):
+        return self.cfg_sdf.encoding.type == "hashgrid"
+
+    def _levels_in_use(self):
+        c2f = self.cfg_sdf.encoding.coarse2fine
+        return self.active_levels if c2f.enabled else self.cfg_sdf.encoding.levels
+
+    def encode_rows(self, points_flat, taps=((0.0, 0.0, 0.0),)):
+        """[T,N,3+LD]: xyz ++ masked features at points + taps (one launch)."""
+        enc = self.tcnn_encoding
+        pts = points_flat.float().contiguous()
+        if torch.is_grad_enabled() and enc.params.requires_grad:
+            return _EncodeRows.apply(pts, enc.params, enc, self._unit_map, self._levels_in_use(), tuple(taps))
+        return _EncodeRows.forward(_NoCtx(), pts, enc.params.detach(), enc, self._unit_map, self._levels_in_use(),
+                                   tuple(taps))
+
+    def forward(self, points_3D, with_sdf=True, with_feat=True):
+        points_enc = self.encode(points_3D)  # [...,3+LD]
+        sdf, feat = self.mlp(points_enc, with_sdf=with_sdf, with_feat=with_feat)
+        return sdf, feat  # [...,1],[...,K]
+
+    def sdf(self, points_3D):
+        return self.forward(points_3D, with_sdf=True, with_feat=False)[0]
+
+    def encode(self, points_3D):
+        if self._hashgrid():
+            rows = self.encode_rows(points_3D.reshape(-1, 3))[0]
+            return rows.view(*points_3D.shape[:-1], rows.shape[-1])
+        if self.cfg_sdf.encoding.type != "fourier":
+            raise NotImplementedError("Unknown encoding type")
+        points_enc = positional_encoding(points_3D, num_freq_bases=self.cfg_sdf.encoding.levels)
+        if self.cfg_sdf.encoding.coarse2fine.enabled:
+            mask = torch.zeros_like(points_enc)
+            mask[..., :(self.active_levels * 6)] = 1
+            points_enc = points_enc * mask
+        return torch.cat([points_3D, points_enc], dim=-1)
+
+    def set_active_levels(self, current_iter=None):
+        anneal_levels = max((current_iter - self.warm_up_end) // self.cfg_sdf.encoding.coarse2fine.step, 1)
+        self.anneal_levels = min(self.cfg_sdf.encoding.levels, anneal_levels)
+        self.active_levels = max(self.cfg_sdf.encoding.coarse2fine.init_active_level, self.anneal_levels)
+
+    def set_normal_epsilon(self):
+        if self.cfg_sdf.encoding.coarse2fine.enabled:
+            epsilon_res = self.resolutions[self.anneal_levels - 1]
+        else:
+            epsilon_res = self.resolutions[-1]
+        self.normal_eps = 1. / epsilon_res
+
+    def _tap_offsets(self):
+        taps = self.cfg_sdf.gradient.taps
+        if taps == 6:
+            e = float(np.float32(self.normal_eps))  # torch.tensor([eps,0,0], dtype=float32), modules.py:135-137
+            return e, ((e, 0, 0), (-e, 0, 0), (0, e, 0), (0, -e, 0), (0, 0, e), (0, 0, -e))
+        if taps == 4:
+            eps = self.normal_eps / np.sqrt(3)  # modules.py:158
+            e = float(np.float32(eps))          # k * eps is evaluated in float32 (k is a float32 tensor)
+            return eps, ((e, -e, -e), (-e, -e, e), (-e, e, -e), (e, e, e))
+        raise ValueError("Only support 4 or 6 taps.")
+
+    def compute_gradients(self, x, training=False, sdf=None):
+        """modules.py:115-178.  Note: hessian is the diagonal (6 taps) or trace/3 replicated (4 taps)."""
+        mode = self.cfg_sdf.gradient.mode
+        if mode == "analytical":
+            raise NotImplementedError("analytical gradients need the encode's second derivative; the shipped "
+                                      "default (base.yaml:67-68) is numerical")
+        if mode != "numerical":
+            raise ValueError(mode)
+        eps, offsets = self._tap_offsets()
+        if self._hashgrid():
+            rows = self.encode_rows(x.reshape(-1, 3), taps=offsets)                 # [T,N,3+LD], one encode launch
+            s = self.mlp(rows, with_sdf=True, with_feat=False)[0]                    # [T,N,1], one MLP pass
+            s = [t.view(*x.shape[:-1], 1) for t in s.unbind(0)]
+        else:
+            s = [self.sdf(x + torch.tensor(o, dtype=x.dtype, device=x.device)) for o in offsets]
+        hessian = None
+        if self.cfg_sdf.gradient.taps == 6:
+            gradient = torch.cat([(s[0] - s[1]) / (2 * eps), (s[2] - s[3]) / (2 * eps), (s[4] - s[5]) / (2 * eps)], dim=-1)
+            if training:
+                assert sdf is not None
+                hessian = torch.cat([(s[0] + s[1] - 2 * sdf) / (eps ** 2), (s[2] + s[3] - 2 * sdf) / (eps ** 2),
+                                     (s[4] + s[5] - 2 * sdf) / (eps ** 2)], dim=-1)
+        else:
+            k = [torch.tensor(v, dtype=x.dtype, device=x.device) for v in ((1, -1, -1), (-1, -1, 1), (-1, 1, -1), (1, 1, 1))]
+            gradient = (k[0] * s[0] + k[1] * s[1] + k[2] * s[2] + k[3] * s[3]) / (4.0 * eps)
+            if training:
+                assert sdf is not None
+                hessian_xx = ((s[0] + s[1] + s[2] + s[3]) / 2.0 - 2 * sdf) / eps ** 2
+                hessian = torch.cat([hessian_xx, hessian_xx, hessian_xx], dim=-1) / 3.0
+        return gradient, hessian
+
+
+class _NoCtx:
+    """Stand-in for the autograd context when the encode runs without gradient tracking."""
+    needs_input_grad = (False,) * 6
+
+    def save_for_backward(self, *a):
+        pass
+
+
+class NeuralRGB(torch.nn.Module):
+
+    def __init__(self, cfg_rgb, feat_dim, appear_embed):
+        super().__init__()
+        self.cfg_rgb = cfg_rgb
+        self.cfg_appear_embed = appear_embed
+        encoding_view_dim = self.build_encoding(cfg_rgb.encoding_view)
+        input_base_dim = 6 if cfg_rgb.mode == "idr" else 3
+        input_dim = input_base_dim + encoding_view_dim + feat_dim + (appear_embed.dim if appear_embed.enabled else 0)
+        self.build_mlp(cfg_rgb.mlp, input_dim=input_dim)
+
+    def build_encoding(self, cfg_encoding_view):
+        if cfg_encoding_view.type == "fourier":
+            return 6 * cfg_encoding_view.levels
+        if cfg_encoding_view.type == "spherical":
+            self.spherical_harmonic_encoding = partial(get_spherical_harmonics, levels=cfg_encoding_view.levels)
+            return (cfg_encoding_view.levels + 1) ** 2
+        raise NotImplementedError("Unknown encoding type")
+
+    def build_mlp(self, cfg_mlp, input_dim=3):
+        layer_dims = [input_dim] + [cfg_mlp.hidden_dim] * cfg_mlp.num_layers + [3]
+        activ = get_activation(cfg_mlp.activ, **cfg_mlp.activ_params)
+        self.mlp = MLPwithSkipConnection(layer_dims, skip_connection=cfg_mlp.skip, activ=activ,
+                                         use_weightnorm=cfg_mlp.weight_norm)
+
+    def forward(self, points_3D, normals, rays_unit, feats, app):
+        view_enc = self.encode_view(rays_unit)
+        input_list = [points_3D, view_enc, normals, feats]
+        if app is not None:
+            input_list.append(app)
+        if self.cfg_rgb.mode == "no_view_dir":
+            input_list = [t for t in input_list if t is not view_enc]
+        if self.cfg_rgb.mode == "no_normal":
+            input_list = [t for t in input_list if t is not normals]
+        return self.mlp(torch.cat(input_list, dim=-1)).sigmoid()
+
+    def encode_view(self, rays_unit):
+        if self.cfg_rgb.encoding_view.type == "fourier":
+            return positional_encoding(rays_unit, num_freq_bases=self.cfg_rgb.encoding_view.levels)
+        if self.cfg_rgb.encoding_view.type == "spherical":
+            return self.spherical_harmonic_encoding(rays_unit)
+        raise NotImplementedError("Unknown encoding type")
+
+
+class BackgroundNeRF(torch.nn.Module):
+
+    def __init__(self, cfg_background, appear_embed):
+        super().__init__()
+        self.cfg_background = cfg_background
+        self.cfg_appear_embed = appear_embed
+        encoding_dim, encoding_view_dim = self.build_encoding(cfg_background.encoding, cfg_background.encoding_view)
+        input_dim = 4 + encoding_dim
+        input_view_dim = cfg_background.mlp.hidden_dim + encoding_view_dim + \
+            (appear_embed.dim if appear_embed.enabled else 0)
+        self.build_mlp(cfg_background.mlp, input_dim=input_dim, input_view_dim=input_view_dim)
+
+    def build_encoding(self, cfg_encoding, cfg_encoding_view):
+        if cfg_encoding.type != "fourier":
+            raise NotImplementedError("Unknown encoding type")
+        encoding_dim = 8 * cfg_encoding.levels
+        if cfg_encoding_view.type == "fourier":
+            encoding_view_dim = 6 * cfg_encoding_view.levels
+        elif cfg_encoding_view.type == "spherical":
+            self.spherical_harmonic_encoding = partial(get_spherical_harmonics, levels=cfg_encoding_view.levels)
+            encoding_view_dim = (cfg_encoding_view.levels + 1) ** 2
+        else:
+            raise NotImplementedError("Unknown encoding type")
+        return encoding_dim, encoding_view_dim
+
+    def build_mlp(self, cfg_mlp, input_dim=3, input_view_dim=3):
+        activ = get_activation(cfg_mlp.activ, **cfg_mlp.activ_params)
+        layer_dims = [input_dim] + [cfg_mlp.hidden_dim] * (cfg_mlp.num_layers - 1) + [cfg_mlp.hidden_dim + 1]
+        self.mlp_feat = MLPwithSkipConnection(layer_dims, skip_connection=cfg_mlp.skip, activ=activ)
+        self.activ_density = get_activation(cfg_mlp.activ_density, **cfg_mlp.activ_density_params)
+        layer_dims_rgb = [input_view_dim] + [cfg_mlp.hidden_dim_rgb] * (cfg_mlp.num_layers_rgb - 1) + [3]
+        self.mlp_rgb = MLPwithSkipConnection(layer_dims_rgb, skip_connection=cfg_mlp.skip_rgb, activ=activ)
+
+    def forward(self, points_3D, rays_unit, app_outside):
+        points_enc = self.encode(points_3D)
+        out = self.mlp_feat(points_enc)
+        density, feat = self.activ_density(out[..., 0]), self.mlp_feat.activ(out[..., 1:])
+        if not self.cfg_background.view_dep:
+            raise NotImplementedError
+        input_list = [feat, self.encode_view(rays_unit)]
+        if app_outside is not None:
+            input_list.append(app_outside)
+        rgb = self.mlp_rgb(torch.cat(input_list, dim=-1)).sigmoid()
+        return rgb, density
+
+    def encode(self, points_3D):
+        # inverted-sphere reparametrisation (x/|x|, 1/|x|), modules.py:289-292
+        norm = points_3D.norm(dim=-1, keepdim=True)
+        points = torch.cat([points_3D / norm, 1.0 / norm], dim=-1)
+        if self.cfg_background.encoding.type != "fourier":
+            raise NotImplementedError("Unknown encoding type")
+        return torch.cat([points, positional_encoding(points, num_freq_bases=self.cfg_background.encoding.levels)], dim=-1)
+
+    def encode_view(self, rays_unit):
+        if self.cfg_background.encoding_view.type == "fourier":
+            return positional_encoding(rays_unit, num_freq_bases=self.cfg_background.encoding_view.levels)
+        if self.cfg_background.encoding_view.type == "spherical":
+            return self.spherical_harmonic_encoding(rays_unit)
+        raise NotImplementedError("Unknown encoding type")

@@ -95,6 +95,99 @@ def render_fixtures():
     print("wrote render_golden.npz with", len(out), "arrays")
 
 
+def small_model_config(taps):
+    """A scaled-down base.yaml `model:` section (4 hash-grid levels, 64-wide MLPs) so that the fixture stays small."""
+    from neuralangelo_b200.config import AttrDict
+    return AttrDict(
+        object=dict(
+            sdf=dict(mlp=dict(num_layers=1, hidden_dim=64, skip=[], activ="softplus", activ_params=dict(beta=100),
+                              geometric_init=True, weight_norm=True, out_bias=0.5, inside_out=False),
+                     encoding=dict(type="hashgrid", levels=4,
+                                   hashgrid=dict(min_logres=2, max_logres=5, dict_size=10, dim=4, range=[-2, 2]),
+                                   coarse2fine=dict(enabled=True, init_active_level=2, step=10)),
+                     gradient=dict(mode="numerical", taps=taps)),
+            rgb=dict(mlp=dict(num_layers=2, hidden_dim=64, skip=[], activ="relu_", activ_params={}, weight_norm=True),
+                     mode="idr", encoding_view=dict(type="spherical", levels=3)),
+            s_var=dict(init_val=3.0, anneal_end=0.1)),
+        background=dict(enabled=True, white=False,
+                        mlp=dict(num_layers=4, hidden_dim=32, skip=[2], num_layers_rgb=2, hidden_dim_rgb=16, skip_rgb=[],
+                                 activ="relu", activ_params={}, activ_density="softplus", activ_density_params={}),
+                        view_dep=True, encoding=dict(type="fourier", levels=4),
+                        encoding_view=dict(type="spherical", levels=3)),
+        render=dict(rand_rays=24, num_samples=dict(coarse=8, fine=4, background=6), num_sample_hierarchy=2,
+                    stratified=False),
+        appear_embed=dict(enabled=False, dim=8))
+
+
+def model_fixtures():
+    """Full `Model.forward` (train mode) + loss gradients of the UNMODIFIED reference model on the CPU, hash grid
+    provided by oracle/tcnn_stub.py.  Stores inputs, the complete state dict, outputs and parameter gradients."""
+    from . import tcnn_stub
+    reference_shim.install(tcnn_module=tcnn_stub)
+    from neuralangelo_b200.config import AttrDict
+    from projects.neuralangelo.model import Model
+    from projects.neuralangelo.utils.misc import eikonal_loss, curvature_loss
+
+    for taps in (4, 6):
+        torch.manual_seed(1234 + taps)
+        cfg_model = small_model_config(taps)
+        cfg_data = AttrDict(num_images=None, train=dict(image_size=[20, 24]), val=dict(image_size=[10, 12]))
+        model = Model(cfg_model, cfg_data)
+        # make the encoding matter: geometric init zeroes its first-layer weights and tcnn's init is +-1e-4
+        with torch.no_grad():
+            model.neural_sdf.tcnn_encoding.params.uniform_(-0.3, 0.3)
+            lin0 = model.neural_sdf.mlp.linears[0]
+            lin0.weight_v[:, 3:] = torch.randn_like(lin0.weight_v[:, 3:]) * 0.05
+        model.train()
+        model.neural_sdf.warm_up_end = 5
+        model.neural_sdf.set_active_levels(35)      # -> anneal 3, active 3 of 4 levels
+        model.neural_sdf.set_normal_epsilon()
+        model.progress = 0.04
+        # two cameras on a radius-3 sphere looking at the origin, wide enough that some rays miss the unit sphere
+        def look_at(eye):
+            eye = torch.tensor(eye, dtype=torch.float32)
+            fwd = -eye / eye.norm()
+            right = torch.linalg.cross(torch.tensor([0.0, 1.0, 0.0]), fwd)
+            right = right / right.norm()
+            up = torch.linalg.cross(fwd, right)
+            R = torch.stack([right, up, fwd], dim=0)    # world -> camera rotation
+            return torch.cat([R, (-R @ eye)[:, None]], dim=1)
+        pose = torch.stack([look_at([0.3, 0.2, -3.0]), look_at([2.0, 0.5, 2.2])])
+        intr = torch.tensor([[36.0, 0.0, 12.0], [0.0, 36.0, 10.0], [0.0, 0.0, 1.0]]).repeat(2, 1, 1)
+        g = torch.Generator().manual_seed(99)
+        ray_idx = torch.stack([torch.randperm(20 * 24, generator=g)[:24] for _ in range(2)])
+        target = torch.rand(2, 24, 3, generator=g)
+        if taps == 4:
+            # whole forward() incl. ray generation, one image (with B > 1 the reference's own `.view(-1, 3)` at
+            # modules.py:84 fails on the CPU: slice_by_ray_idx returns a ray-major layout there)
+            pose, intr, ray_idx, target = pose[:1], intr[:1], ray_idx[:1], target[:1]
+            out = model(dict(pose=pose, intr=intr, idx=torch.arange(1), ray_idx=ray_idx))
+        else:
+            # two images through render_rays with explicitly contiguous rays
+            from projects.nerf.utils import camera as ref_camera, nerf_util as ref_nerf_util
+            center, ray = ref_camera.get_center_and_ray(pose, intr, [20, 24])
+            center = ref_nerf_util.slice_by_ray_idx(center, ray_idx).contiguous()
+            ray = ref_nerf_util.slice_by_ray_idx(ray, ray_idx).contiguous()
+            out = model.render_rays(center, torch.nn.functional.normalize(ray, dim=-1), sample_idx=torch.arange(2),
+                                    stratified=False)
+        loss = 3 * torch.nn.functional.l1_loss(out["rgb"], target) + 0.1 * eikonal_loss(out["gradients"], out["outside"]) \
+            + 5e-4 * curvature_loss(out["hessians"], out["outside"])
+        loss.backward()
+        fx = {"in_pose": _np(pose), "in_intr": _np(intr), "in_ray_idx": _np(ray_idx), "in_target": _np(target),
+              "loss": _np(loss), "normal_eps": np.float64(model.neural_sdf.normal_eps),
+              "active_levels": np.int64(model.neural_sdf.active_levels)}
+        for k in ("rgb", "dists", "weights", "gradients", "hessians", "outside"):
+            fx["out_" + k] = _np(out[k])
+        for k, v in model.state_dict().items():
+            fx["sd_" + k] = _np(v)
+        for k, p in model.named_parameters():
+            fx["grad_" + k] = _np(p.grad) if p.grad is not None else np.zeros(0, dtype=np.float32)
+        np.savez_compressed(os.path.join(OUT, f"model_golden_taps{taps}.npz"), **fx)
+        print(f"wrote model_golden_taps{taps}.npz: loss {float(loss):.6f}, outside rays {int(out['outside'].sum())},",
+              "table grad nnz", int((model.neural_sdf.tcnn_encoding.params.grad != 0).sum()))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     render_fixtures()
+    model_fixtures()

@@ -38,10 +38,12 @@ def install(tcnn_module=None):
     for name in ("mcubes", "trimesh"):
         if name not in sys.modules:
             sys.modules[name] = types.ModuleType(name)
-    if tcnn_module is not None:
-        sys.modules["tinycudann"] = tcnn_module
-    elif "tinycudann" not in sys.modules:
-        sys.modules["tinycudann"] = types.ModuleType("tinycudann")
+    if tcnn_module is None:
+        from . import tcnn_stub as tcnn_module  # pure-torch hash grid (oracle/tcnn_stub.py)
+    sys.modules["tinycudann"] = tcnn_module
+    mod = sys.modules.get("projects.neuralangelo.utils.modules")
+    if mod is not None:
+        mod.tcnn = tcnn_module
     import torch
     from projects.nerf.utils import nerf_util
     if not isinstance(nerf_util.sample_dists, functools.partial):
