@@ -204,6 +204,22 @@ int na_mc_run_static(const float* volume, int nx, int ny, int nz, double iso, do
                      const double* origin /* host [3] or NULL */, double* verts, int64_t cap_verts,
                      int32_t* faces, int64_t cap_faces, uint32_t* counts, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Optimizer step.
+ * One fused pass of AdamW (decoupled weight decay, bias-corrected, no amsgrad -- torch.optim.AdamW's
+ * update rule) over a flat fp32 buffer: p, exp_avg, exp_avg_sq updated in place; grads are multiplied
+ * by grad_scale before use (1/world_size when they hold a cross-rank SUM) and, if zero_grad != 0, cleared.
+ * `step` is the 1-based step count used for the bias corrections.  Buffers 16-byte aligned.
+ * Replaces: torch.optim.AdamW.step + optimizer.zero_grad as wired at
+ *   imaginaire/trainers/utils/get_trainer.py:106-150 and imaginaire/trainers/base.py:454-457.
+ * ---------------------------------------------------------------------------------------- */
+int na_adamw_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                  float beta2, float eps, float weight_decay, int64_t step, float grad_scale, int zero_grad,
+                  void* stream);
+/* params[i] *= factor: applies the accumulated weight decay of hash-grid levels that were inactive
+ * (zero gradient, zero moments: AdamW reduces to p *= 1 - lr*wd per step) when they become active. */
+int na_scale_inplace(float* params, int64_t n, float factor, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

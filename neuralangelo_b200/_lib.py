@@ -76,6 +76,8 @@ def _declare(lib):
         "na_mc_static_max_cells": (ctypes.c_int64, []),
         "na_mc_run_static": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double,
                                             ctypes.c_double, ctypes.POINTER(ctypes.c_double), vp, i64, vp, i64, vp, vp]),
+        "na_adamw_step": (ctypes.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, f32, ctypes.c_int, vp]),
+        "na_scale_inplace": (ctypes.c_int, [vp, i64, f32, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -1,0 +1,121 @@
+"""Fused AdamW over flat parameter buffers (csrc/optim.cu), the optimizer of the reference
+(`imaginaire/trainers/utils/get_trainer.py:106-150`, base.yaml:117-121) restricted to what its
+Neuralangelo config uses (AdamW, one param group, no amsgrad).
+
+Layout: every parameter except the hash table is re-homed into ONE flat fp32 buffer (`param.data` becomes a
+view of it) with a matching flat gradient buffer pre-assigned as `param.grad`, so the optimizer step, the
+gradient zeroing and the data-parallel all-reduce are each one launch.  The hash table keeps its own buffer
+(1.46 GB); its gradient buffer is persistent and the encode backward scatters straight into it.
+
+Hash-table levels that are not yet active (coarse-to-fine, modules.py:97-100) have identically zero
+gradient and zero moments, for which AdamW reduces to p *= (1 - lr*wd) per step; those levels are skipped
+and the accumulated factor is applied when a level becomes active (equal to the step-by-step product up to
+fp32 rounding).
+"""
+import math
+
+import torch
+
+from . import _lib
+from ._lib import ptr
+
+_L = _lib.lib
+
+
+class FusedAdamW:
+    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, lazy_inactive_levels=True):
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.step_count = 0
+        self.lazy = lazy_inactive_levels
+        self.model = model
+        self.encoding = getattr(getattr(model, "neural_sdf", None), "tcnn_encoding", None)
+        table = self.encoding.params if self.encoding is not None else None
+        small = [p for p in model.parameters() if p.requires_grad and p is not table]
+        dev = small[0].device
+        n = sum(p.numel() for p in small)
+        n_pad = (n + 3) // 4 * 4
+        self.flat_p = torch.zeros(n_pad, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros_like(self.flat_p)
+        self.flat_m = torch.zeros_like(self.flat_p)
+        self.flat_v = torch.zeros_like(self.flat_p)
+        off = 0
+        for p in small:
+            k = p.numel()
+            self.flat_p[off:off + k].copy_(p.data.reshape(-1))
+            p.data = self.flat_p[off:off + k].view_as(p)
+            p.grad = self.flat_g[off:off + k].view_as(p)
+            off += k
+        self.n_small = n
+        self.small_params = small
+        self.table = table
+        if table is not None:
+            self.encoding.accumulate_grad_in_place = True
+            if table.grad is None:
+                table.grad = torch.zeros_like(table)
+            self.table_m = torch.zeros_like(table)
+            self.table_v = torch.zeros_like(table)
+            self.n_levels = self.encoding.desc.n_levels
+            self.level_end = [(self.encoding.desc.offset[l] + self.encoding.desc.entries[l]) * self.encoding.desc.n_features
+                              for l in range(self.n_levels)]
+            self.applied_levels = self.n_levels if not self.lazy else 0  # levels whose decay is up to date
+            self.pending_log_decay = 0.0  # log of prod (1 - lr*wd) over the steps skipped by inactive levels
+
+    def active_prefix(self):
+        """Number of table parameters in active levels (a prefix: levels are stored coarse to fine)."""
+        if self.table is None:
+            return 0
+        sdf = self.model.neural_sdf
+        active = sdf.active_levels if sdf.cfg_sdf.encoding.coarse2fine.enabled else self.n_levels
+        return self.level_end[min(active, self.n_levels) - 1], min(active, self.n_levels)
+
+    def grad_views(self):
+        """(small flat grad, active table grad prefix) -- the two tensors a data-parallel reduce must sum."""
+        if self.table is None:
+            return self.flat_g, None
+        n_active, _ = self.active_prefix()
+        return self.flat_g, self.table.grad[:n_active]
+
+    def step(self, grad_scale=1.0, lr=None):
+        lr = self.lr if lr is None else lr
+        self.step_count += 1
+        b1, b2 = self.betas
+        stream = _lib.current_stream()
+        _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
+                                      self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
+                                      grad_scale, 1, stream), "na_adamw_step")
+        if self.table is None:
+            return
+        n_active, active = self.active_prefix()
+        if not self.lazy:
+            n_active, active = self.table.numel(), self.n_levels
+        if active > self.applied_levels:
+            # newly activated levels catch up on the weight decay of the steps they sat out (all inactive levels
+            # share one history -- none has ever been active -- so a single running product is exact)
+            lo = self.level_end[self.applied_levels - 1] if self.applied_levels > 0 else 0
+            hi = self.level_end[active - 1]
+            if self.pending_log_decay != 0.0:
+                _lib.check(_L().na_scale_inplace(ptr(self.table[lo:]), hi - lo, math.exp(self.pending_log_decay), stream),
+                           "na_scale_inplace")
+            self.applied_levels = active
+        _lib.check(_L().na_adamw_step(ptr(self.table), ptr(self.table.grad), ptr(self.table_m), ptr(self.table_v),
+                                      n_active, lr, b1, b2, self.eps, self.weight_decay, self.step_count, grad_scale, 1,
+                                      stream), "na_adamw_step")
+        if self.lazy and self.applied_levels < self.n_levels:
+            self.pending_log_decay += math.log1p(-lr * self.weight_decay)
+
+    def flush_inactive_decay(self):
+        """Bring the still-inactive levels up to date (call before saving a checkpoint)."""
+        if self.table is None or not self.lazy or self.applied_levels >= self.n_levels:
+            return
+        lo = self.level_end[self.applied_levels - 1] if self.applied_levels > 0 else 0
+        if self.pending_log_decay != 0.0:
+            _lib.check(_L().na_scale_inplace(ptr(self.table[lo:]), self.table.numel() - lo,
+                                             math.exp(self.pending_log_decay), _lib.current_stream()), "na_scale_inplace")
+        self.pending_log_decay = 0.0
+
+    def zero_grad(self):
+        """Gradients are cleared by step(); this is for the case no step was taken."""
+        self.flat_g.zero_()
+        if self.table is not None:
+            n_active, _ = self.active_prefix()
+            self.table.grad[:n_active].zero_()
