@@ -220,6 +220,22 @@ int na_adamw_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq
  * (zero gradient, zero moments: AdamW reduces to p *= 1 - lr*wd per step) when they become active. */
 int na_scale_inplace(float* params, int64_t n, float factor, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Fused SDF MLP forward on tcgen05 tensor cores (accumulators in TMEM, activations stay on chip):
+ *   h0 = softplus_beta(x W0^T + b0);  sdf = h0 . w_head + b_head;  [feat = softplus_beta(h0 W1^T + b1)]
+ * x: [m, k0] fp32 rows with stride ldx (e.g. the [N,131] rows of the encode).  n = hidden width
+ * (64/128/192/256).  Weights are the EFFECTIVE (weight-norm already applied) matrices split into two fp16
+ * pieces and packed K-chunk-major: w_hi/w_lo[(k/8)][(j/8)][j%8][k%8] for W[j,k], K zero-padded to
+ * k0_pad (multiple of 16, <= 256) for layer 0 and to n for layer 1; w_lo = (W - float(w_hi)) * 2048.
+ * Outputs are optional (NULL): sdf_out [m]; feat_out [m,n] (needs n_layers == 2); hidden_out [m,n] = h0.
+ * Replaces: MLPforNeuralSDF.forward, projects/neuralangelo/utils/mlp.py:55-69 (num_layers = 1), behind
+ *   NeuralSDF.forward / .sdf, projects/neuralangelo/utils/modules.py:68-74.
+ * ---------------------------------------------------------------------------------------- */
+int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, int n, int n_layers, const void* w0_hi,
+                   const void* w0_lo, const float* b0, int k0_pad, const void* w1_hi, const void* w1_lo,
+                   const float* b1, const float* w_head, float b_head, float beta, float* sdf_out, float* feat_out,
+                   int64_t ld_feat, float* hidden_out, int64_t ld_hidden, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

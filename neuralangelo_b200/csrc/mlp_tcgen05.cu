@@ -1,0 +1,412 @@
+// Fused SDF MLP forward on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM).
+//
+// Replaces, for the geometry network, the chain
+//   WN-Linear(3+LD -> H) -> softplus(beta) -> [Linear(H -> 1) = SDF]  [-> WN-Linear(H -> H) -> softplus = feature]
+// of projects/neuralangelo/utils/mlp.py:55-69 (MLPforNeuralSDF.forward with the default `num_layers: 1`),
+// i.e. the cuBLAS + eager elementwise launches behind NeuralSDF.forward / .sdf (modules.py:68-74).
+//
+// Precision.  The finite-difference normals and curvature (modules.py:132-175) amplify SDF rounding by
+// 1/(2 eps) and 1/eps^2, so single-pass TF32/BF16 tensor-core products are not good enough.  Every operand
+// is split into two fp16 pieces, a = a_hi + 2^-11 a_lo' with a_lo' = (a - a_hi) * 2^11 (the scaling keeps the
+// low piece out of fp16's subnormal range), and three kind::f16 MMAs per k-step accumulate in fp32:
+//     D_main  += A_hi B_hi                       D_cross += A_lo' B_hi + A_hi B_lo'
+// result = D_main + 2^-11 D_cross (the dropped a_lo b_lo term is 2^-22 relative) -- fp32-grade products at
+// 1.5x the cost of one TF32 pass.
+//
+// Structure (one CTA per SM, persistent over 128-row tiles; M = 128, N = H <= 256, cta_group::1):
+//   warps 0-7  compute: stage the input tile into shared memory as fp16 hi/lo in the UMMA core-matrix order,
+//              then per layer read the accumulators back (tcgen05.ld), add bias, softplus, take the SDF head's
+//              dot product on the fly, and write the activations straight back to shared memory as the next
+//              layer's A operand -- intermediate activations never touch HBM;
+//   warp 8     MMA issuer (one elected lane issues tcgen05.mma, tcgen05.commit signals mbarriers);
+//   warp 9     weight loader: cp.async.bulk (TMA, 1-D) streams pre-packed 32-wide K blocks of W_hi / W_lo
+//              through a 3-stage ring, running ahead across layers and tiles.
+// Operands are K-major without swizzle: element (row, k) of a tile with R rows sits at
+//     (k / 8) * (R / 8 * 128) + (row / 8) * 128 + (row % 8) * 16 + (k % 8) * 2   bytes,
+// so a thread that owns one row writes its eight-column chunks with conflict-free 16-byte stores and the
+// host packs the weights once per optimiser step into the exact shared-memory image.
+#include "na_common.cuh"
+#include <cuda_fp16.h>
+
+namespace {
+
+constexpr int kTileM = 128;
+constexpr int kComputeWarps = 8;
+constexpr int kComputeThreads = kComputeWarps * 32;
+constexpr int kThreads = kComputeThreads + 64;  // + MMA warp + loader warp
+constexpr int kStages = 3;
+constexpr int kBlockK = 32;                     // K elements per weight-ring stage
+constexpr int kMaxK = 256;                      // widest A operand held in shared memory
+constexpr int kMaxN = 256;
+constexpr float kLoScale = 2048.f, kLoInv = 1.f / 2048.f;
+
+constexpr int kABytes = kTileM * kMaxK * 2;             // one fp16 A image (hi or lo): 64 KB
+constexpr int kBStageBytes = 2 * kMaxN * kBlockK * 2;   // W_hi block + W_lo block: 32 KB
+constexpr int kSmemBytes = 2 * kABytes + kStages * kBStageBytes + 2 * kTileM * 4 + 1024;
+
+struct Layer {
+    const __half* w_hi;   // packed [K_pad/8][N/8][8][8]
+    const __half* w_lo;
+    const float* bias;    // [N]
+    int k_pad;            // multiple of 16, <= 256
+};
+
+struct MlpParams {
+    const float* x;       // [M, K0] rows, row stride ldx floats
+    int64_t ldx;
+    int64_t m;
+    int k0;               // valid input columns (<= layer[0].k_pad)
+    int n;                // hidden width: multiple of 64, <= 256
+    int n_layers;         // 1 (SDF only) or 2 (SDF + feature)
+    Layer layer[2];
+    const float* w_head;  // [N] SDF head weights (applied to layer 0's activations) or null
+    float b_head;
+    float beta;           // softplus beta
+    float* sdf_out;       // [M] or null
+    float* feat_out;      // [M, N] rows, stride ld_feat, or null
+    int64_t ld_feat;
+    float* hidden_out;    // [M, N] layer-0 activations (for the backward), stride ld_hidden, or null
+    int64_t ld_hidden;
+};
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// Bounded wait: a protocol bug must trap, not hang the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (spin > (1u << 24)) __trap();
+    }
+}
+__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                           uint32_t accumulate) {
+    asm volatile(
+        "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,"
+        "%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, no swizzle: LBO = byte stride between core matrices adjacent in K, SBO = between 8-row groups.
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
+    return d;                // layout type 0 (no swizzle), base offset 0
+}
+
+__device__ __forceinline__ uint32_t make_idesc(int m, int n) {
+    // c_format F32 (bits 4-5 = 1), a/b format F16 (0), both K-major (0), N>>3 at bit 17, M>>4 at bit 24
+    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void split_f16(float v, __half& hi, __half& lo) {
+    v = fminf(fmaxf(v, -65504.f), 65504.f);
+    hi = __float2half_rn(v);
+    lo = __float2half_rn((v - __half2float(hi)) * kLoScale);
+}
+
+__device__ __forceinline__ uint32_t pack2(__half a, __half b) {
+    return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
+}
+
+__device__ __forceinline__ float softplus(float x, float beta) {
+    const float bx = beta * x;
+    return bx > 20.f ? x : log1pf(expf(bx)) / beta;  // torch.nn.functional.softplus, threshold 20
+}
+
+// Byte offset of the 16-byte chunk holding (row, k..k+7) inside an A image of kTileM rows.
+__device__ __forceinline__ uint32_t a_chunk_offset(int row, int kchunk) {
+    return (uint32_t)kchunk * (kTileM / 8 * 128) + (uint32_t)(row >> 3) * 128 + (uint32_t)(row & 7) * 16;
+}
+
+// ---------------------------------------------------------------- the kernel
+__global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_constant__ MlpParams P) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* a_hi = smem;
+    uint8_t* a_lo = smem + kABytes;
+    uint8_t* b_ring = smem + 2 * kABytes;
+    float* head_partial = reinterpret_cast<float*>(b_ring + kStages * kBStageBytes);  // [2][kTileM]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(head_partial + 2 * kTileM);
+    // bars: [0,S) b_full, [S,2S) b_empty, 2S a_ready, 2S+1 d_ready; then the TMEM base address word
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 2);
+    const uint32_t bar0 = smem_u32(bars);
+    auto b_full = [&](int s) { return bar0 + 8u * s; };
+    auto b_empty = [&](int s) { return bar0 + 8u * (kStages + s); };
+    const uint32_t a_ready = bar0 + 8u * (2 * kStages), d_ready = bar0 + 8u * (2 * kStages + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = P.n;
+    const int64_t n_tiles = (P.m + kTileM - 1) / kTileM;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(b_full(s), 1);
+            mbar_init(b_empty(s), 1);
+        }
+        mbar_init(a_ready, kComputeThreads);
+        mbar_init(d_ready, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == kComputeWarps) {  // MMA warp owns the TMEM allocation: D_main [0,256) and D_cross [256,512)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t d_main = tmem_base, d_cross = tmem_base + 256;
+
+    if (warp == kComputeWarps + 1) {
+        // ===================== weight loader =====================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                for (int l = 0; l < P.n_layers; ++l) {
+                    const Layer& L = P.layer[l];
+                    const int chunks = L.k_pad / 8;                // 8-wide k-chunks in this layer
+                    const uint32_t chunk_bytes = (uint32_t)n * 16;  // N/8 core matrices of 128 B
+                    for (int c0 = 0; c0 < chunks; c0 += kBlockK / 8, ++it) {
+                        const int s = it % kStages;
+                        const uint32_t ph = (it / kStages) & 1;
+                        mbar_wait(b_empty(s), ph ^ 1);
+                        const int nc = min(kBlockK / 8, chunks - c0);
+                        const uint32_t bytes = nc * chunk_bytes;
+                        mbar_expect_tx(b_full(s), 2 * bytes);
+                        const uint32_t dst = smem_u32(b_ring + s * kBStageBytes);
+                        bulk_copy_g2s(dst, reinterpret_cast<const uint8_t*>(L.w_hi) + (size_t)c0 * chunk_bytes, bytes,
+                                      b_full(s));
+                        bulk_copy_g2s(dst + kBStageBytes / 2,
+                                      reinterpret_cast<const uint8_t*>(L.w_lo) + (size_t)c0 * chunk_bytes, bytes,
+                                      b_full(s));
+                    }
+                }
+            }
+        }
+    } else if (warp == kComputeWarps) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(kTileM, n);
+            const uint32_t a_lbo = kTileM / 8 * 128, b_lbo = (uint32_t)n / 8 * 128;
+            uint32_t it = 0, layer_it = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                for (int l = 0; l < P.n_layers; ++l, ++layer_it) {
+                    const Layer& L = P.layer[l];
+                    mbar_wait(a_ready, layer_it & 1);
+                    tc_fence_after();
+                    const int chunks = L.k_pad / 8;
+                    bool first = true;
+                    for (int c0 = 0; c0 < chunks; c0 += kBlockK / 8, ++it) {
+                        const int s = it % kStages;
+                        mbar_wait(b_full(s), (it / kStages) & 1);
+                        tc_fence_after();
+                        const int nc = min(kBlockK / 8, chunks - c0);
+                        const uint32_t b_hi_addr = smem_u32(b_ring + s * kBStageBytes);
+                        const uint32_t b_lo_addr = b_hi_addr + kBStageBytes / 2;
+                        for (int c = 0; c < nc; c += 2) {  // one UMMA k-step = 16 elements = 2 chunks
+                            const uint32_t a_off = (uint32_t)(c0 + c) * a_lbo, b_off = (uint32_t)c * b_lbo;
+                            const uint64_t ah = make_desc(smem_u32(a_hi) + a_off, a_lbo, 128);
+                            const uint64_t al = make_desc(smem_u32(a_lo) + a_off, a_lbo, 128);
+                            const uint64_t bh = make_desc(b_hi_addr + b_off, b_lbo, 128);
+                            const uint64_t bl = make_desc(b_lo_addr + b_off, b_lbo, 128);
+                            tc_mma_f16(d_cross, al, bh, idesc, first ? 0u : 1u);
+                            tc_mma_f16(d_cross, ah, bl, idesc, 1u);
+                            tc_mma_f16(d_main, ah, bh, idesc, first ? 0u : 1u);
+                            first = false;
+                        }
+                        tc_commit(b_empty(s));  // frees the ring slot once the MMAs above have read it
+                    }
+                    tc_commit(d_ready);  // accumulators complete (and A no longer being read)
+                }
+            }
+        }
+    } else {
+        // ===================== compute warps =====================
+        const int tid = threadIdx.x;                // 0..255
+        const int quarter = warp & 3;               // TMEM lane quarter this warp may access
+        const int half = warp >> 2;                 // which half of the N columns this warp handles
+        const int row = quarter * 32 + lane;        // accumulator row == TMEM lane
+        const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+        uint32_t layer_it = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const int64_t row0 = tile * kTileM;
+            // ---- stage the input tile: fp32 rows -> fp16 hi / lo chunks
+            {
+                const int chunks = P.layer[0].k_pad / 8;
+                for (int idx = tid; idx < kTileM * chunks; idx += kComputeThreads) {
+                    const int r = idx / chunks, kc = idx % chunks;
+                    const int64_t gr = row0 + r;
+                    uint32_t hi[4], lo[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        float v[2];
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int col = kc * 8 + j * 2 + e;
+                            v[e] = (gr < P.m && col < P.k0) ? __ldg(P.x + gr * P.ldx + col) : 0.f;
+                        }
+                        __half h0, l0, h1, l1;
+                        split_f16(v[0], h0, l0);
+                        split_f16(v[1], h1, l1);
+                        hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                    }
+                    const uint32_t off = a_chunk_offset(r, kc);
+                    *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                    *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                }
+            }
+            fence_proxy_async();
+            mbar_arrive(a_ready);
+
+            for (int l = 0; l < P.n_layers; ++l, ++layer_it) {
+                const bool last = l == P.n_layers - 1;
+                const bool head = (l == 0) && P.w_head != nullptr;
+                mbar_wait(d_ready, layer_it & 1);
+                tc_fence_after();
+                const float* bias = P.layer[l].bias;
+                float dot = 0.f;
+                const int col_begin = half * (n / 2), col_end = col_begin + n / 2;
+                for (int c0 = col_begin; c0 < col_end; c0 += 32) {
+                    uint32_t rm[32], rc[32];
+                    tc_ld32(d_main + lane_addr + c0, rm);
+                    tc_ld32(d_cross + lane_addr + c0, rc);
+                    tc_wait_ld();
+                    float act[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float pre = fmaf(__uint_as_float(rc[j]), kLoInv, __uint_as_float(rm[j])) + __ldg(bias + c0 + j);
+                        act[j] = softplus(pre, P.beta);
+                        if (head) dot = fmaf(act[j], __ldg(P.w_head + c0 + j), dot);
+                    }
+                    if (!last) {  // next layer's A operand, straight back to shared memory
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint32_t hi[4], lo[4];
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                __half h0, l0, h1, l1;
+                                split_f16(act[q * 8 + j * 2], h0, l0);
+                                split_f16(act[q * 8 + j * 2 + 1], h1, l1);
+                                hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                            }
+                            const uint32_t off = a_chunk_offset(row, c0 / 8 + q);
+                            *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                            *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                        }
+                    }
+                    float* dst = nullptr;
+                    if (last && l == 1 && P.feat_out) dst = P.feat_out + (row0 + row) * P.ld_feat + c0;
+                    if (l == 0 && P.hidden_out) dst = P.hidden_out + (row0 + row) * P.ld_hidden + c0;
+                    if (dst && row0 + row < P.m) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4)
+                            *reinterpret_cast<float4*>(dst + j) = make_float4(act[j], act[j + 1], act[j + 2], act[j + 3]);
+                    }
+                }
+                if (head) {
+                    head_partial[half * kTileM + row] = dot;
+                    asm volatile("bar.sync 1, %0;" ::"n"(kComputeThreads) : "memory");
+                    if (half == 0 && row0 + row < P.m && P.sdf_out)
+                        P.sdf_out[row0 + row] = head_partial[row] + head_partial[kTileM + row] + P.b_head;
+                    asm volatile("bar.sync 1, %0;" ::"n"(kComputeThreads) : "memory");
+                }
+                tc_fence_before();
+                if (!last) {
+                    fence_proxy_async();
+                    mbar_arrive(a_ready);
+                }
+            }
+            // all TMEM reads of this tile are done before the next tile's first MMA overwrites the accumulators:
+            // the next a_ready arrival (after the input staging above) orders them.
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kComputeWarps) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+}  // namespace
+
+extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, int n, int n_layers,
+                              const void* w0_hi, const void* w0_lo, const float* b0, int k0_pad, const void* w1_hi,
+                              const void* w1_lo, const float* b1, const float* w_head, float b_head, float beta,
+                              float* sdf_out, float* feat_out, int64_t ld_feat, float* hidden_out, int64_t ld_hidden,
+                              void* stream) {
+    na::clear_error();
+    NA_REQUIRE(m >= 0, "sdf_mlp_fwd: negative row count");
+    if (m == 0) return NA_OK;
+    NA_REQUIRE(x && w0_hi && w0_lo && b0, "sdf_mlp_fwd: null pointer");
+    NA_REQUIRE(n % 64 == 0 && n >= 64 && n <= kMaxN, "sdf_mlp_fwd: hidden width %d unsupported (64, 128, 192, 256)", n);
+    NA_REQUIRE(k0 >= 1 && k0 <= k0_pad && k0_pad % 16 == 0 && k0_pad <= kMaxK,
+               "sdf_mlp_fwd: k0=%d k0_pad=%d unsupported (k0_pad multiple of 16, <= %d)", k0, k0_pad, kMaxK);
+    NA_REQUIRE(n_layers == 1 || (n_layers == 2 && w1_hi && w1_lo && b1), "sdf_mlp_fwd: n_layers must be 1 or 2");
+    NA_REQUIRE(beta > 0.f, "sdf_mlp_fwd: softplus beta must be positive");
+    NA_REQUIRE(!feat_out || (n_layers == 2 && ld_feat % 4 == 0 && (uintptr_t)feat_out % 16 == 0),
+               "sdf_mlp_fwd: feat_out needs n_layers == 2, 16-byte alignment and a stride multiple of 4");
+    NA_REQUIRE(!hidden_out || (ld_hidden % 4 == 0 && (uintptr_t)hidden_out % 16 == 0),
+               "sdf_mlp_fwd: hidden_out needs 16-byte alignment and a stride multiple of 4");
+    NA_REQUIRE(((uintptr_t)w0_hi | (uintptr_t)w0_lo | (uintptr_t)w1_hi | (uintptr_t)w1_lo) % 16 == 0,
+               "sdf_mlp_fwd: packed weights must be 16-byte aligned");
+    MlpParams P{};
+    P.x = x, P.ldx = ldx, P.m = m, P.k0 = k0, P.n = n, P.n_layers = n_layers;
+    P.layer[0] = Layer{(const __half*)w0_hi, (const __half*)w0_lo, b0, k0_pad};
+    P.layer[1] = Layer{(const __half*)w1_hi, (const __half*)w1_lo, b1, n};
+    P.w_head = w_head, P.b_head = b_head, P.beta = beta;
+    P.sdf_out = sdf_out, P.feat_out = feat_out, P.ld_feat = ld_feat, P.hidden_out = hidden_out, P.ld_hidden = ld_hidden;
+    if (int rc = na::check_cuda(cudaFuncSetAttribute(sdf_mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                     kSmemBytes),
+                                "cudaFuncSetAttribute(sdf_mlp_fwd_kernel)"))
+        return rc;
+    const int64_t tiles = (m + kTileM - 1) / kTileM;
+    const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
+    sdf_mlp_fwd_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);
+    NA_CHECK_LAUNCH("sdf_mlp_fwd_kernel");
+    return NA_OK;
+}
