@@ -19,8 +19,8 @@
 //              dot product on the fly, and write the activations straight back to shared memory as the next
 //              layer's A operand -- intermediate activations never touch HBM;
 //   warp 8     MMA issuer (one elected lane issues tcgen05.mma, tcgen05.commit signals mbarriers);
-//   warp 9     weight loader: cp.async.bulk (TMA, 1-D) streams pre-packed 32-wide K blocks of W_hi / W_lo
-//              through a 3-stage ring, running ahead across layers and tiles.
+//   warp 9     weight loader: cp.async.bulk (TMA, 1-D) streams pre-packed 16-wide K blocks of W_hi / W_lo
+//              through a 5-stage ring, running ahead across layers and tiles.
 // Operands are K-major without swizzle: element (row, k) of a tile with R rows sits at
 //     (k / 8) * (R / 8 * 128) + (row / 8) * 128 + (row % 8) * 16 + (k % 8) * 2   bytes,
 // so a thread that owns one row writes its eight-column chunks with conflict-free 16-byte stores and the
@@ -34,15 +34,15 @@ constexpr int kTileM = 128;
 constexpr int kComputeWarps = 8;
 constexpr int kComputeThreads = kComputeWarps * 32;
 constexpr int kThreads = kComputeThreads + 64;  // + MMA warp + loader warp
-constexpr int kStages = 3;
-constexpr int kBlockK = 32;                     // K elements per weight-ring stage
+constexpr int kStages = 5;
+constexpr int kBlockK = 16;                     // K elements per weight-ring stage (one UMMA k-step)
 constexpr int kMaxK = 256;                      // widest A operand held in shared memory
 constexpr int kMaxN = 256;
 constexpr float kLoScale = 2048.f, kLoInv = 1.f / 2048.f;
 
 constexpr int kABytes = kTileM * kMaxK * 2;             // one fp16 A image (hi or lo): 64 KB
 constexpr int kBStageBytes = 2 * kMaxN * kBlockK * 2;   // W_hi block + W_lo block: 32 KB
-constexpr int kSmemBytes = 2 * kABytes + kStages * kBStageBytes + 2 * kTileM * 4 + 1024;
+constexpr int kSmemBytes = 2 * kABytes + kStages * kBStageBytes + 2 * kTileM * 4 + 3 * kMaxN * 4 + 1024;
 
 struct Layer {
     const __half* w_hi;   // packed [K_pad/8][N/8][8][8]
@@ -150,9 +150,11 @@ __device__ __forceinline__ uint32_t pack2(__half a, __half b) {
     return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
 }
 
-__device__ __forceinline__ float softplus(float x, float beta) {
-    const float bx = beta * x;
-    return bx > 20.f ? x : log1pf(expf(bx)) / beta;  // torch.nn.functional.softplus, threshold 20
+// softplus_beta(x) = max(x,0) + log(1 + exp(-|beta x|)) / beta.  Differs from torch's thresholded form
+// (x when beta*x > 20) by < exp(-20)/beta; the fast exp/log intrinsics are accurate to ~1e-7 ABSOLUTE on the
+// log term, i.e. ~1e-9 on the result for beta = 100 -- far below the fp32 rounding of the sums around it.
+__device__ __forceinline__ float softplus(float x, float beta, float inv_beta) {
+    return fmaxf(x, 0.f) + __logf(1.f + __expf(-fabsf(beta * x))) * inv_beta;
 }
 
 // Byte offset of the 16-byte chunk holding (row, k..k+7) inside an A image of kTileM rows.
@@ -167,7 +169,9 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
     uint8_t* a_lo = smem + kABytes;
     uint8_t* b_ring = smem + 2 * kABytes;
     float* head_partial = reinterpret_cast<float*>(b_ring + kStages * kBStageBytes);  // [2][kTileM]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(head_partial + 2 * kTileM);
+    float* s_bias = head_partial + 2 * kTileM;   // [2][kMaxN] per-layer biases
+    float* s_head = s_bias + 2 * kMaxN;           // [kMaxN] SDF head weights
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_head + kMaxN);
     // bars: [0,S) b_full, [S,2S) b_empty, 2S a_ready, 2S+1 d_ready; then the TMEM base address word
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 2);
     const uint32_t bar0 = smem_u32(bars);
@@ -179,6 +183,11 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
     const int n = P.n;
     const int64_t n_tiles = (P.m + kTileM - 1) / kTileM;
 
+    for (int i = threadIdx.x; i < n; i += kThreads) {
+        s_bias[i] = P.layer[0].bias[i];
+        s_bias[kMaxN + i] = P.n_layers > 1 ? P.layer[1].bias[i] : 0.f;
+        s_head[i] = P.w_head ? P.w_head[i] : 0.f;
+    }
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(b_full(s), 1);
@@ -273,29 +282,43 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
         uint32_t layer_it = 0;
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
             const int64_t row0 = tile * kTileM;
-            // ---- stage the input tile: fp32 rows -> fp16 hi / lo chunks
+            // ---- stage the input tile: fp32 rows -> fp16 hi / lo chunks.  Consecutive threads take consecutive
+            // 8-column chunks of a row (coalesced 32-byte reads); all of a thread's loads are issued before any
+            // conversion so that their latencies overlap.
             {
                 const int chunks = P.layer[0].k_pad / 8;
-                for (int idx = tid; idx < kTileM * chunks; idx += kComputeThreads) {
-                    const int r = idx / chunks, kc = idx % chunks;
-                    const int64_t gr = row0 + r;
-                    uint32_t hi[4], lo[4];
+                const int total = kTileM * chunks;
+                constexpr int kPerThread = kTileM * (kMaxK / 8) / kComputeThreads;  // 16
+#pragma unroll 1
+                for (int base = 0; base < kPerThread; base += 4) {
+                    float v[4][8];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        float v[2];
+                    for (int u = 0; u < 4; ++u) {
+                        const int idx = (base + u) * kComputeThreads + tid;
+                        const int r = idx / chunks, kc = idx - r * chunks;
+                        const int64_t gr = row0 + r;
+                        const float* src = P.x + gr * P.ldx + kc * 8;
 #pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const int col = kc * 8 + j * 2 + e;
-                            v[e] = (gr < P.m && col < P.k0) ? __ldg(P.x + gr * P.ldx + col) : 0.f;
-                        }
-                        __half h0, l0, h1, l1;
-                        split_f16(v[0], h0, l0);
-                        split_f16(v[1], h1, l1);
-                        hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                        for (int e = 0; e < 8; ++e)
+                            v[u][e] = (idx < total && gr < P.m && kc * 8 + e < P.k0) ? __ldg(src + e) : 0.f;
                     }
-                    const uint32_t off = a_chunk_offset(r, kc);
-                    *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                    *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int idx = (base + u) * kComputeThreads + tid;
+                        if (idx >= total) continue;
+                        const int r = idx / chunks, kc = idx - r * chunks;
+                        uint32_t hi[4], lo[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            __half h0, l0, h1, l1;
+                            split_f16(v[u][2 * j], h0, l0);
+                            split_f16(v[u][2 * j + 1], h1, l1);
+                            hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                        }
+                        const uint32_t off = a_chunk_offset(r, kc);
+                        *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                        *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                    }
                 }
             }
             fence_proxy_async();
@@ -306,7 +329,8 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
                 const bool head = (l == 0) && P.w_head != nullptr;
                 mbar_wait(d_ready, layer_it & 1);
                 tc_fence_after();
-                const float* bias = P.layer[l].bias;
+                const float* bias = s_bias + l * kMaxN;
+                const float inv_beta = 1.f / P.beta;
                 float dot = 0.f;
                 const int col_begin = half * (n / 2), col_end = col_begin + n / 2;
                 for (int c0 = col_begin; c0 < col_end; c0 += 32) {
@@ -317,9 +341,9 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
                     float act[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
-                        const float pre = fmaf(__uint_as_float(rc[j]), kLoInv, __uint_as_float(rm[j])) + __ldg(bias + c0 + j);
-                        act[j] = softplus(pre, P.beta);
-                        if (head) dot = fmaf(act[j], __ldg(P.w_head + c0 + j), dot);
+                        const float pre = fmaf(__uint_as_float(rc[j]), kLoInv, __uint_as_float(rm[j])) + bias[c0 + j];
+                        act[j] = softplus(pre, P.beta, inv_beta);
+                        if (head) dot = fmaf(act[j], s_head[c0 + j], dot);
                     }
                     if (!last) {  // next layer's A operand, straight back to shared memory
 #pragma unroll
