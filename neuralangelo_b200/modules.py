@@ -113,8 +113,39 @@ class NeuralSDF(torch.nn.Module):
 
     def forward(self, points_3D, with_sdf=True, with_feat=True):
         points_enc = self.encode(points_3D)  # [...,3+LD]
-        sdf, feat = self.mlp(points_enc, with_sdf=with_sdf, with_feat=with_feat)
+        sdf, feat = self.run_mlp(points_enc, with_sdf=with_sdf, with_feat=with_feat)
         return sdf, feat  # [...,1],[...,K]
+
+    # ---- MLP dispatch: tcgen05 fused kernel when no autograd graph is needed, torch ops otherwise ----------
+    def invalidate_packed_weights(self):
+        """Call after the MLP weights changed through a path torch cannot see (the fused optimizer kernel)."""
+        self._weights_epoch = getattr(self, "_weights_epoch", 0) + 1
+
+    def _packed_mlp(self):
+        from .fused_mlp import PackedSdfMlp
+        key = (getattr(self, "_weights_epoch", 0),) + tuple(p._version for p in self.mlp.parameters()) + \
+            (next(self.mlp.parameters()).device,)
+        if getattr(self, "_packed_key", None) != key:
+            try:
+                self._packed = PackedSdfMlp(self.mlp, beta=self.cfg_sdf.mlp.activ_params.get("beta", 1.0)) \
+                    if self.cfg_sdf.mlp.activ == "softplus" else None
+            except NotImplementedError:
+                self._packed = None  # architecture outside the fused kernel's envelope: torch ops
+            self._packed_key = key
+        return self._packed
+
+    def run_mlp(self, rows, with_sdf=True, with_feat=True):
+        """rows [...,3+LD] -> [sdf [...,1] | None, feat [...,K] | None]."""
+        needs_graph = torch.is_grad_enabled() and (rows.requires_grad or any(p.requires_grad for p in self.mlp.parameters()))
+        packed = None if needs_graph or not rows.is_cuda else self._packed_mlp()
+        if packed is None:
+            return self.mlp(rows, with_sdf=with_sdf, with_feat=with_feat)
+        flat = rows.reshape(-1, rows.shape[-1])
+        if flat.stride(-1) != 1 or flat.dtype != torch.float32:
+            flat = flat.float().contiguous()
+        sdf, feat = packed.forward(flat, with_sdf=with_sdf, with_feat=with_feat)
+        lead = rows.shape[:-1]
+        return [sdf.view(*lead, 1) if sdf is not None else None, feat.view(*lead, -1) if feat is not None else None]
 
     def sdf(self, points_3D):
         return self.forward(points_3D, with_sdf=True, with_feat=False)[0]
@@ -166,7 +197,7 @@ class NeuralSDF(torch.nn.Module):
         eps, offsets = self._tap_offsets()
         if self._hashgrid():
             rows = self.encode_rows(x.reshape(-1, 3), taps=offsets)                 # [T,N,3+LD], one encode launch
-            s = self.mlp(rows, with_sdf=True, with_feat=False)[0]                    # [T,N,1], one MLP pass
+            s = self.run_mlp(rows, with_sdf=True, with_feat=False)[0]                # [T,N,1], one MLP pass
             s = [t.view(*x.shape[:-1], 1) for t in s.unbind(0)]
         else:
             s = [self.sdf(x + torch.tensor(o, dtype=x.dtype, device=x.device)) for o in offsets]

@@ -83,6 +83,9 @@ class FusedAdamW:
         _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
                                       self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
                                       grad_scale, 1, stream), "na_adamw_step")
+        sdf_mod = getattr(self.model, "neural_sdf", None)
+        if sdf_mod is not None and hasattr(sdf_mod, "invalidate_packed_weights"):
+            sdf_mod.invalidate_packed_weights()   # the kernel above rewrote the MLP weights behind torch's back
         if self.table is None:
             return
         n_active, active = self.active_prefix()

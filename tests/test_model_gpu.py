@@ -101,3 +101,23 @@ def test_inference_outputs(na_lib, cuda_device, golden_dir):
     assert out["depth_map"].shape == (1, 1, 10, 12) and out["opacity_map"].shape == (1, 1, 10, 12)
     assert torch.isfinite(out["rgb_map"]).all() and out["opacity_map"].max() <= 1 + 1e-5
     assert "hessians" not in out or out["hessians"] is None
+
+
+def test_no_grad_sdf_uses_fused_mlp_and_matches_autograd_path(na_lib, cuda_device, golden_dir):
+    """NeuralSDF.sdf / forward under no_grad run the tcgen05 MLP; values must agree with the torch-op path."""
+    G = _load(golden_dir, 6)
+    model = _build(G, 6, cuda_device)
+    pts = (torch.rand(2, 50, 7, 3, generator=torch.Generator().manual_seed(0)) * 2 - 1).to(cuda_device)
+    sdf_graph, feat_graph = model.neural_sdf(pts)                 # autograd path (torch ops)
+    with torch.no_grad():
+        sdf_fused, feat_fused = model.neural_sdf(pts)            # fused kernel
+        assert model.neural_sdf._packed is not None
+        only = model.neural_sdf.sdf(pts)
+    torch.testing.assert_close(sdf_fused, sdf_graph.detach(), rtol=0, atol=3e-6)
+    torch.testing.assert_close(feat_fused, feat_graph.detach(), rtol=0, atol=3e-6)
+    torch.testing.assert_close(only, sdf_fused, rtol=0, atol=1e-7)
+    # weights changed in place -> the packed copy must be rebuilt
+    with torch.no_grad():
+        model.neural_sdf.mlp.linear_sdf.bias.add_(0.25)
+        shifted = model.neural_sdf.sdf(pts)
+    torch.testing.assert_close(shifted, only + 0.25, rtol=0, atol=1e-6)
