@@ -245,6 +245,9 @@ def run_ours(args, rank, local_rank, world):
         t = torch.tensor([elapsed_ms, e2e_ms], device=dev, dtype=torch.float64)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         elapsed_ms, e2e_ms = t.tolist()
+    del out, dout, dtable, table, pts_dev
+    torch.cuda.empty_cache()
+    extras = {} if args.no_extras else collect_extras(args, rank, world, dev)
     if rank != 0:
         return
     ms_per_step = elapsed_ms / args.steps
@@ -274,6 +277,7 @@ def run_ours(args, rank, local_rank, world):
                      "other_kernels": {"hashgrid_taps_fwd_kernel": {"ms": fwd_ms, "GBps": fwd_bytes / fwd_ms / 1e6},
                                        "hashgrid_taps_bwd_kernel": {"ms": bwd_ms, "GBps": bwd_bytes / bwd_ms / 1e6}}},
     }
+    line["extras"] = extras
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
         n_sample = 1 << 17
@@ -284,6 +288,119 @@ def run_ours(args, rank, local_rank, world):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------------------------------------
+# secondary measurements carried in "extras" (BASELINE.json configs[2..4]); never allowed to break the main line
+# ------------------------------------------------------------------------------------------------
+def _look_at(eye):
+    eye = torch.tensor(eye, dtype=torch.float32)
+    fwd = -eye / eye.norm()
+    right = torch.linalg.cross(torch.tensor([0.0, 1.0, 0.0]), fwd)
+    right = right / right.norm()
+    R = torch.stack([right, torch.linalg.cross(fwd, right), fwd])
+    return torch.cat([R, (-R @ eye)[:, None]], dim=1)
+
+
+def extra_train_step(rank, world, dev, steps=30, warmup=8, taps=4, force_all_levels=True):
+    """BASELINE.json configs[2]/[3]: full training step of the default hash-grid config (16 levels, 2^22, dim 8),
+    synthetic cameras (32 poses on a radius-3 sphere, 800x800, focal 1111), random-init weights, 512 rays per
+    GPU per step, batch pose/intrinsics/ray indices/target colours arriving from pinned host memory, gradients
+    all-reduced across ranks.  Returns aggregate rays/s."""
+    from neuralangelo_b200.config import default_data_config, default_model_config
+    from neuralangelo_b200.model import Model
+    from neuralangelo_b200.trainer import TrainStep
+    torch.manual_seed(0)
+    cfg = default_model_config()
+    cfg.object.sdf.gradient.taps = taps
+    model = Model(cfg, default_data_config()).to(dev)
+    ts = TrainStep(model, max_iter=500000, warm_up_end=5000)
+    if force_all_levels:
+        ts.current_iteration = 5000 + 16 * 5000
+    g = torch.Generator().manual_seed(1000 + rank)
+    poses = []
+    for _ in range(32):
+        v = torch.randn(3, generator=g)
+        poses.append(_look_at((v / v.norm() * 3.0).tolist()))
+    intr = torch.tensor([[1111.0, 0, 400.0], [0, 1111.0, 400.0], [0, 0, 1.0]])
+    host = [dict(pose=poses[i % 32][None].pin_memory(), intr=intr[None].pin_memory(),
+                 idx=torch.tensor([i % 32]).pin_memory(),
+                 ray_idx=torch.randint(0, 640000, (1, 512), generator=g).pin_memory(),
+                 image_sampled=torch.rand(1, 512, 3, generator=g).pin_memory()) for i in range(8)]
+
+    def step(i):
+        data = {k: v.to(dev, non_blocking=True) for k, v in host[i % 8].items()}
+        return ts.step(data)
+
+    for i in range(warmup):
+        step(i)
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        loss = step(i)
+    loss_host = float(loss)            # device->host read of the step's result
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / steps
+    if world > 1:
+        t = torch.tensor([dt], device=dev, dtype=torch.float64)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        dt = float(t)
+    del ts, model
+    torch.cuda.empty_cache()
+    return {"rays_per_s": 512 * world / dt, "ms_per_step": dt * 1e3, "rays_per_gpu": 512, "taps": taps,
+            "active_levels": 16 if force_all_levels else 4, "last_loss": loss_host, "timing": "host clock around "
+            "synchronised steps, max over ranks; includes H2D of the batch and the gradient all-reduce"}
+
+
+def extra_mesh(rank, world, dev, res=512):
+    """BASELINE.json configs[4] at reduced resolution (the full 2048^3 takes ~30 s on one GPU): blocked SDF
+    query of the default hash-grid model + marching cubes, blocks sharded across ranks, gathered on rank 0."""
+    from neuralangelo_b200 import mesh
+    from neuralangelo_b200.config import default_model_config
+    from neuralangelo_b200.modules import NeuralSDF
+    torch.manual_seed(0)
+    net = NeuralSDF(default_model_config().object.sdf).to(dev).eval()
+    net.warm_up_end = 5000
+    net.set_active_levels(500000)
+    bounds = np.array([[-1.0, 1.0]] * 3)
+    fn = lambda x: -net.sdf(x)
+    mesh.extract_mesh(fn, bounds, intv=2.0 / 128, block_res=128)   # warm-up
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    m = mesh.extract_mesh(fn, bounds, intv=2.0 / res, block_res=128)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dt], device=dev, dtype=torch.float64)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        dt = float(t)
+    g = mesh.LatticeGrid(bounds, 2.0 / res, 128)
+    npts = sum(int(np.prod([len(a) for a in g.block_axes(i)])) for i in range(len(g)))
+    out = {"resolution": res, "block_res": 128, "seconds": dt, "lattice_points": npts, "Mpoints_per_s": npts / dt / 1e6,
+           "projected_2048_cubed_seconds": dt * (2063.0 ** 3) / npts}
+    if m is not None:
+        out.update(vertices=len(m.vertices), faces=len(m.faces))
+    del net
+    torch.cuda.empty_cache()
+    return out
+
+
+def collect_extras(args, rank, world, dev):
+    extras = {}
+    for name, fn in (("train_step", lambda: extra_train_step(rank, world, dev)),
+                     ("train_step_4_active_levels", lambda: extra_train_step(rank, world, dev, force_all_levels=False)),
+                     ("mesh_extract", lambda: extra_mesh(rank, world, dev))):
+        try:
+            extras[name] = fn()
+        except Exception as e:  # noqa: BLE001 -- extras must never break the headline line
+            extras[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    return extras
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -292,6 +409,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="encode", choices=["encode"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the secondary train-step / mesh measurements")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", 0))
