@@ -236,6 +236,20 @@ int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, int n, int n_
                    const float* b1, const float* w_head, float b_head, float beta, float* sdf_out, float* feat_out,
                    int64_t ld_feat, float* hidden_out, int64_t ld_hidden, void* stream);
 
+/* Backward of na_sdf_mlp_fwd with respect to the input rows, plus the pre-activation gradients from which
+ * the caller forms the weight gradients (dW1 = dz1^T h0, dW0 = dz0^T x, db = column sums):
+ *   dz1 = d_feat * s'(z1);  dh0 = dz1 W1 + d_sdf w_head;  dz0 = dh0 * s'(z0);  dx = dz0 W0.
+ * two_layer = 0 is the SDF-only form (finite-difference taps): dz0 = d_sdf w_head * s'(z0), dx = dz0 W0.
+ * hidden / feat are the activations saved by the forward ([m,n], stride ld_act); row_bound[m] >= max_j |d_feat[r,j]|
+ * (used to scale each row into fp16 range); w1t / w0t are W1^T and W0^T (rows zero-padded to k0_pad) packed
+ * like the forward weights; w1_colsum_max = max_j sum_k |W1[k,j]|, w_head_absmax = max |w_head|.
+ * Replaces: the autograd backward of MLPforNeuralSDF.forward (projects/neuralangelo/utils/mlp.py:55-69). */
+int na_sdf_mlp_bwd(int64_t m, int n, int k0, int k0_pad, int two_layer, const float* d_sdf, const float* d_feat,
+                   const float* feat, const float* hidden, int64_t ld_act, const float* row_bound,
+                   const void* w1t_hi, const void* w1t_lo, const void* w0t_hi, const void* w0t_lo,
+                   const float* w_head, float beta, float w1_colsum_max, float w_head_absmax, float* dz1, float* dz0,
+                   float* dx, int64_t ld_dx, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -396,6 +396,304 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
     }
 }
 
+
+// ==================================================================================================
+// Backward of the same MLP with respect to its INPUT rows (the gradient that the hash-grid backward
+// scatters into the table) and the pre-activation gradients dz0 / dz1 from which the host forms the weight
+// gradients (dW = dz^T a: reductions over all rows, left to a library GEMM in round 1).
+//
+//   dz1 = d_feat * s'(z1)                      s'(z) = 1 - exp(-beta * softplus(z))  (from the saved activation)
+//   dh0 = dz1 W1 + d_sdf w_head
+//   dz0 = dh0 * s'(z0)
+//   dx  = dz0 W0
+// Same pipeline as the forward: the two products run on tcgen05 with split-fp16 operands; the elementwise
+// links run in the accumulator epilogues and hand the next A operand over in shared memory.  Gradients are
+// tiny (1e-9 .. 1e-4), far below fp16's range, so every row is multiplied by a power of two derived from a
+// cheap upper bound of its magnitude before it is split, and the product is scaled back in the epilogue
+// (row scaling commutes with the right-multiplication by W).
+// ==================================================================================================
+struct BwdParams {
+    int64_t m;
+    int n;                 // hidden width
+    int k0, k0_pad;        // input width (valid, padded to 16)
+    int two_layer;         // 1: feature branch present (d_feat / feat / W1), 0: SDF-only rows (taps)
+    const float* d_sdf;    // [M] or null
+    const float* d_feat;   // [M,N] (stride ld_act) or null
+    const float* feat;     // [M,N] layer-1 activations
+    const float* hidden;   // [M,N] layer-0 activations
+    int64_t ld_act;
+    const float* row_bound;  // [M] upper bound of |d_feat| per row (two_layer only)
+    Layer w1t;             // packed W1^T: B[n_in][k_out]; k_pad = n
+    Layer w0t;             // packed W0^T: B[col][k_hidden] with col padded to k0_pad; k_pad = n
+    const float* w_head;   // [N]
+    float beta;
+    float w1_colsum_max;   // max_j sum_k |W1[k,j]|   (bound of |dz1 W1| per unit |dz1|)
+    float w_head_absmax;
+    float* dz1;            // [M,N] out (two_layer), stride ld_act
+    float* dz0;            // [M,N] out, stride ld_act
+    float* dx;             // [M,k0] out, stride ld_dx
+    int64_t ld_dx;
+};
+
+__device__ __forceinline__ float pow2_scale(float bound) {
+    // largest power of two s with s * bound <= 2^14 (fp16 max is 2^16 - 32); bound == 0 -> 1
+    if (!(bound > 0.f)) return 1.f;
+    int e;
+    frexpf(bound, &e);  // bound = f * 2^e, f in [0.5,1)
+    e = 14 - e;
+    e = e > 120 ? 120 : (e < -120 ? -120 : e);
+    return ldexpf(1.f, e);
+}
+
+__global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_constant__ BwdParams P) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* a_hi = smem;
+    uint8_t* a_lo = smem + kABytes;
+    uint8_t* b_ring = smem + 2 * kABytes;
+    float* s_head = reinterpret_cast<float*>(b_ring + kStages * kBStageBytes);  // [kMaxN]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_head + kMaxN);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 2);
+    const uint32_t bar0 = smem_u32(bars);
+    auto b_full = [&](int s) { return bar0 + 8u * s; };
+    auto b_empty = [&](int s) { return bar0 + 8u * (kStages + s); };
+    const uint32_t a_ready = bar0 + 8u * (2 * kStages), d_ready = bar0 + 8u * (2 * kStages + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = P.n;
+    const int n_mma = P.two_layer ? 2 : 1;
+    const int64_t n_tiles = (P.m + kTileM - 1) / kTileM;
+
+    for (int i = threadIdx.x; i < n; i += kThreads) s_head[i] = P.w_head[i];
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(b_full(s), 1);
+            mbar_init(b_empty(s), 1);
+        }
+        mbar_init(a_ready, kComputeThreads);
+        mbar_init(d_ready, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == kComputeWarps) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t d_main = tmem_base, d_cross = tmem_base + 256;
+
+    if (warp == kComputeWarps + 1) {
+        // ===================== weight loader: per tile [W1^T] then W0^T =====================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                for (int g = 0; g < n_mma; ++g) {
+                    const bool is_w1 = P.two_layer && g == 0;
+                    const Layer& L = is_w1 ? P.w1t : P.w0t;
+                    const int n_out = is_w1 ? n : P.k0_pad;
+                    const int chunks = n / 8;  // K = hidden width for both products
+                    const uint32_t chunk_bytes = (uint32_t)n_out * 16;
+                    for (int c0 = 0; c0 < chunks; c0 += kBlockK / 8, ++it) {
+                        const int s = it % kStages;
+                        mbar_wait(b_empty(s), ((it / kStages) & 1) ^ 1);
+                        const uint32_t bytes = (kBlockK / 8) * chunk_bytes;
+                        mbar_expect_tx(b_full(s), 2 * bytes);
+                        const uint32_t dst = smem_u32(b_ring + s * kBStageBytes);
+                        bulk_copy_g2s(dst, reinterpret_cast<const uint8_t*>(L.w_hi) + (size_t)c0 * chunk_bytes, bytes,
+                                      b_full(s));
+                        bulk_copy_g2s(dst + kBStageBytes / 2,
+                                      reinterpret_cast<const uint8_t*>(L.w_lo) + (size_t)c0 * chunk_bytes, bytes,
+                                      b_full(s));
+                    }
+                }
+            }
+        }
+    } else if (warp == kComputeWarps) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t a_lbo = kTileM / 8 * 128;
+            uint32_t it = 0, mma_it = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                for (int g = 0; g < n_mma; ++g, ++mma_it) {
+                    const bool is_w1 = P.two_layer && g == 0;
+                    const int n_out = is_w1 ? n : P.k0_pad;
+                    const uint32_t idesc = make_idesc(kTileM, n_out);
+                    const uint32_t b_lbo = (uint32_t)n_out / 8 * 128;
+                    mbar_wait(a_ready, mma_it & 1);
+                    tc_fence_after();
+                    const int chunks = n / 8;
+                    bool first = true;
+                    for (int c0 = 0; c0 < chunks; c0 += kBlockK / 8, ++it) {
+                        const int s = it % kStages;
+                        mbar_wait(b_full(s), (it / kStages) & 1);
+                        tc_fence_after();
+                        const uint32_t b_hi_addr = smem_u32(b_ring + s * kBStageBytes);
+                        const uint32_t b_lo_addr = b_hi_addr + kBStageBytes / 2;
+                        for (int c = 0; c < kBlockK / 8; c += 2) {
+                            const uint32_t a_off = (uint32_t)(c0 + c) * a_lbo, b_off = (uint32_t)c * b_lbo;
+                            const uint64_t ah = make_desc(smem_u32(a_hi) + a_off, a_lbo, 128);
+                            const uint64_t al = make_desc(smem_u32(a_lo) + a_off, a_lbo, 128);
+                            const uint64_t bh = make_desc(b_hi_addr + b_off, b_lbo, 128);
+                            const uint64_t bl = make_desc(b_lo_addr + b_off, b_lbo, 128);
+                            tc_mma_f16(d_cross, al, bh, idesc, first ? 0u : 1u);
+                            tc_mma_f16(d_cross, ah, bl, idesc, 1u);
+                            tc_mma_f16(d_main, ah, bh, idesc, first ? 0u : 1u);
+                            first = false;
+                        }
+                        tc_commit(b_empty(s));
+                    }
+                    tc_commit(d_ready);
+                }
+            }
+        }
+    } else {
+        // ===================== compute warps =====================
+        const int quarter = warp & 3, half = warp >> 2;
+        const int row = quarter * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+        const float beta = P.beta;
+        uint32_t mma_it = 0;
+        // write 32 consecutive values of this thread's row (scaled) as four fp16 hi/lo chunks of the A operand
+        auto store_a = [&](const float (&v)[32], int c0, float scale) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint32_t hi[4], lo[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    __half h0, l0, h1, l1;
+                    split_f16(v[q * 8 + j * 2] * scale, h0, l0);
+                    split_f16(v[q * 8 + j * 2 + 1] * scale, h1, l1);
+                    hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                }
+                const uint32_t off = a_chunk_offset(row, c0 / 8 + q);
+                *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            }
+        };
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const int64_t grow = tile * kTileM + row;
+            const bool valid = grow < P.m;
+            const float dsdf = (valid && P.d_sdf) ? __ldg(P.d_sdf + grow) : 0.f;
+            const int col_begin = half * (n / 2), col_end = col_begin + n / 2;
+            float scale_a, scale_b;  // row scales of the operands of the first / second product of this tile
+            if (P.two_layer) {
+                const float b1 = valid ? __ldg(P.row_bound + grow) : 0.f;
+                scale_a = pow2_scale(b1);
+                scale_b = pow2_scale(b1 * P.w1_colsum_max + fabsf(dsdf) * P.w_head_absmax);
+                // ---- prologue: dz1 = d_feat * s'(z1) -> HBM (fp32) and A operand (scaled, split)
+                for (int c0 = col_begin; c0 < col_end; c0 += 32) {
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        float4 g = make_float4(0.f, 0.f, 0.f, 0.f), f = g;
+                        if (valid) {
+                            g = __ldg(reinterpret_cast<const float4*>(P.d_feat + grow * P.ld_act + c0 + j));
+                            f = __ldg(reinterpret_cast<const float4*>(P.feat + grow * P.ld_act + c0 + j));
+                        }
+                        v[j] = g.x * (1.f - __expf(-beta * f.x)), v[j + 1] = g.y * (1.f - __expf(-beta * f.y));
+                        v[j + 2] = g.z * (1.f - __expf(-beta * f.z)), v[j + 3] = g.w * (1.f - __expf(-beta * f.w));
+                        if (valid)
+                            *reinterpret_cast<float4*>(P.dz1 + grow * P.ld_act + c0 + j) =
+                                make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    }
+                    store_a(v, c0, scale_a);
+                }
+            } else {
+                scale_a = 1.f;
+                scale_b = pow2_scale(fabsf(dsdf) * P.w_head_absmax);
+                // ---- prologue (SDF-only rows): dz0 = d_sdf w_head * s'(z0)
+                for (int c0 = col_begin; c0 < col_end; c0 += 32) {
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        float4 h = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (valid) h = __ldg(reinterpret_cast<const float4*>(P.hidden + grow * P.ld_act + c0 + j));
+                        v[j] = dsdf * s_head[c0 + j] * (1.f - __expf(-beta * h.x));
+                        v[j + 1] = dsdf * s_head[c0 + j + 1] * (1.f - __expf(-beta * h.y));
+                        v[j + 2] = dsdf * s_head[c0 + j + 2] * (1.f - __expf(-beta * h.z));
+                        v[j + 3] = dsdf * s_head[c0 + j + 3] * (1.f - __expf(-beta * h.w));
+                        if (valid)
+                            *reinterpret_cast<float4*>(P.dz0 + grow * P.ld_act + c0 + j) =
+                                make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    }
+                    store_a(v, c0, scale_b);
+                }
+            }
+            fence_proxy_async();
+            mbar_arrive(a_ready);
+
+            if (P.two_layer) {
+                // ---- epilogue of dz1 W1: dh0 = . / scale_a + d_sdf w_head;  dz0 = dh0 * s'(z0) -> HBM and A operand
+                mbar_wait(d_ready, mma_it & 1);
+                ++mma_it;
+                tc_fence_after();
+                const float inv_a = 1.f / scale_a;
+                for (int c0 = col_begin; c0 < col_end; c0 += 32) {
+                    uint32_t rm[32], rc[32];
+                    tc_ld32(d_main + lane_addr + c0, rm);
+                    tc_ld32(d_cross + lane_addr + c0, rc);
+                    tc_wait_ld();
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        float4 h = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (valid) h = __ldg(reinterpret_cast<const float4*>(P.hidden + grow * P.ld_act + c0 + j));
+                        const float hh[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float dh = fmaf(__uint_as_float(rc[j + e]), kLoInv, __uint_as_float(rm[j + e])) * inv_a +
+                                             dsdf * s_head[c0 + j + e];
+                            v[j + e] = dh * (1.f - __expf(-beta * hh[e]));
+                        }
+                        if (valid)
+                            *reinterpret_cast<float4*>(P.dz0 + grow * P.ld_act + c0 + j) =
+                                make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    }
+                    store_a(v, c0, scale_b);
+                }
+                tc_fence_before();
+                fence_proxy_async();
+                mbar_arrive(a_ready);
+            }
+            // ---- epilogue of dz0 W0: dx = . / scale_b  (k0_pad columns, split between the two warp groups)
+            mbar_wait(d_ready, mma_it & 1);
+            ++mma_it;
+            tc_fence_after();
+            {
+                const float inv_b = 1.f / scale_b;
+                const int n_chunks = (P.k0_pad + 31) / 32;
+                const int first_chunk = half == 0 ? 0 : (n_chunks + 1) / 2;
+                const int last_chunk = half == 0 ? (n_chunks + 1) / 2 : n_chunks;
+                for (int ch = first_chunk; ch < last_chunk; ++ch) {
+                    const int c0 = ch * 32;
+                    uint32_t rm[32], rc[32];
+                    tc_ld32(d_main + lane_addr + c0, rm);
+                    tc_ld32(d_cross + lane_addr + c0, rc);
+                    tc_wait_ld();
+                    if (valid) {
+                        float* dst = P.dx + grow * P.ld_dx + c0;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (c0 + j < P.k0)
+                                dst[j] = fmaf(__uint_as_float(rc[j]), kLoInv, __uint_as_float(rm[j])) * inv_b;
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kComputeWarps) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
 }  // namespace
 
 extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, int n, int n_layers,
@@ -432,5 +730,40 @@ extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, in
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
     sdf_mlp_fwd_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);
     NA_CHECK_LAUNCH("sdf_mlp_fwd_kernel");
+    return NA_OK;
+}
+
+extern "C" int na_sdf_mlp_bwd(int64_t m, int n, int k0, int k0_pad, int two_layer, const float* d_sdf,
+                              const float* d_feat, const float* feat, const float* hidden, int64_t ld_act,
+                              const float* row_bound, const void* w1t_hi, const void* w1t_lo, const void* w0t_hi,
+                              const void* w0t_lo, const float* w_head, float beta, float w1_colsum_max,
+                              float w_head_absmax, float* dz1, float* dz0, float* dx, int64_t ld_dx, void* stream) {
+    na::clear_error();
+    NA_REQUIRE(m >= 0, "sdf_mlp_bwd: negative row count");
+    if (m == 0) return NA_OK;
+    NA_REQUIRE(n % 64 == 0 && n >= 64 && n <= kMaxN, "sdf_mlp_bwd: hidden width %d unsupported", n);
+    NA_REQUIRE(k0 >= 1 && k0 <= k0_pad && k0_pad % 16 == 0 && k0_pad <= kMaxK, "sdf_mlp_bwd: k0=%d k0_pad=%d unsupported",
+               k0, k0_pad);
+    NA_REQUIRE(hidden && w0t_hi && w0t_lo && w_head && dz0 && dx, "sdf_mlp_bwd: null pointer");
+    NA_REQUIRE(!two_layer || (d_feat && feat && row_bound && w1t_hi && w1t_lo && dz1),
+               "sdf_mlp_bwd: the two-layer form needs d_feat, feat, row_bound, W1^T and dz1");
+    NA_REQUIRE(ld_act % 4 == 0 && ((uintptr_t)hidden | (uintptr_t)dz0 | (uintptr_t)dz1 | (uintptr_t)d_feat |
+                                   (uintptr_t)feat) % 16 == 0,
+               "sdf_mlp_bwd: activation tensors need 16-byte alignment and a stride multiple of 4");
+    BwdParams P{};
+    P.m = m, P.n = n, P.k0 = k0, P.k0_pad = k0_pad, P.two_layer = two_layer ? 1 : 0;
+    P.d_sdf = d_sdf, P.d_feat = d_feat, P.feat = feat, P.hidden = hidden, P.ld_act = ld_act, P.row_bound = row_bound;
+    P.w1t = Layer{(const __half*)w1t_hi, (const __half*)w1t_lo, nullptr, n};
+    P.w0t = Layer{(const __half*)w0t_hi, (const __half*)w0t_lo, nullptr, n};
+    P.w_head = w_head, P.beta = beta, P.w1_colsum_max = w1_colsum_max, P.w_head_absmax = w_head_absmax;
+    P.dz1 = dz1, P.dz0 = dz0, P.dx = dx, P.ld_dx = ld_dx;
+    if (int rc = na::check_cuda(cudaFuncSetAttribute(sdf_mlp_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                     kSmemBytes),
+                                "cudaFuncSetAttribute(sdf_mlp_bwd_kernel)"))
+        return rc;
+    const int64_t tiles = (m + kTileM - 1) / kTileM;
+    const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
+    sdf_mlp_bwd_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);
+    NA_CHECK_LAUNCH("sdf_mlp_bwd_kernel");
     return NA_OK;
 }

@@ -73,3 +73,86 @@ class PackedSdfMlp:
                                  ptr(sdf), ptr(feat), self.n, ptr(hidden), self.n, _lib.current_stream())
         _lib.check(rc, "na_sdf_mlp_fwd")
         return (sdf, feat, hidden) if with_hidden else (sdf, feat)
+
+
+class FusedSdfMlpFunction(torch.autograd.Function):
+    """Differentiable fused SDF MLP: forward and input-gradient chain on tcgen05; weight gradients
+    (reductions over all rows) by library GEMMs on the pre-activation gradients the kernel returns.
+    Arguments are the EFFECTIVE weights (torch applies / differentiates the weight-norm reparametrisation)."""
+
+    @staticmethod
+    def forward(ctx, rows, w0, b0, w1, b1, w_head, b_head, beta, with_feat):
+        m, k0 = rows.shape
+        n = w0.shape[0]
+        k0_pad = pad16(k0)
+        with torch.no_grad():
+            w0_hi, w0_lo = pack_weight(w0, k0_pad)
+            w1_hi, w1_lo = pack_weight(w1, n) if with_feat else (None, None)
+        dev = rows.device
+        sdf = torch.empty(m, 1, dtype=torch.float32, device=dev)
+        feat = torch.empty(m, n, dtype=torch.float32, device=dev) if with_feat else None
+        hidden = torch.empty(m, n, dtype=torch.float32, device=dev)
+        b0c, b1c, whc = b0.detach().float().contiguous(), b1.detach().float().contiguous(), \
+            w_head.detach().float().reshape(-1).contiguous()
+        rc = _L().na_sdf_mlp_fwd(ptr(rows), rows.stride(0), m, k0, n, 2 if with_feat else 1, ptr(w0_hi), ptr(w0_lo),
+                                 ptr(b0c), k0_pad, ptr(w1_hi), ptr(w1_lo), ptr(b1c), ptr(whc), float(b_head.detach()),
+                                 float(beta), ptr(sdf), ptr(feat), n, ptr(hidden), n, _lib.current_stream())
+        _lib.check(rc, "na_sdf_mlp_fwd")
+        ctx.save_for_backward(rows, hidden, feat if with_feat else hidden, w0, w1, whc)
+        ctx.beta, ctx.with_feat = float(beta), with_feat
+        if not with_feat:
+            feat = torch.empty(0, device=dev)
+            ctx.mark_non_differentiable(feat)
+        return sdf, feat
+
+    @staticmethod
+    def backward(ctx, d_sdf, d_feat):
+        rows, hidden, feat, w0, w1, w_head = ctx.saved_tensors
+        m, k0 = rows.shape
+        n = w0.shape[0]
+        k0_pad = pad16(k0)
+        dev = rows.device
+        two = ctx.with_feat and d_feat is not None
+        d_sdf = d_sdf.float().contiguous().reshape(-1) if d_sdf is not None else torch.zeros(m, device=dev)
+        with torch.no_grad():
+            w0t = torch.zeros(k0_pad, n, dtype=torch.float32, device=dev)
+            w0t[:k0] = w0.detach().float().t()
+            w0t_hi, w0t_lo = pack_weight(w0t, n)
+            if two:
+                d_feat = d_feat.float().contiguous()
+                w1t_hi, w1t_lo = pack_weight(w1.detach().float().t().contiguous(), n)
+                bound = d_feat.abs().amax(dim=1).contiguous()
+                colsum = float(w1.detach().abs().sum(dim=0).max())
+                dz1 = torch.empty(m, n, dtype=torch.float32, device=dev)
+            else:
+                w1t_hi = w1t_lo = bound = dz1 = None
+                colsum = 0.0
+            dz0 = torch.empty(m, n, dtype=torch.float32, device=dev)
+            dx = torch.empty(m, k0, dtype=torch.float32, device=dev)
+            rc = _L().na_sdf_mlp_bwd(m, n, k0, k0_pad, 1 if two else 0, ptr(d_sdf), ptr(d_feat) if two else None,
+                                     ptr(feat) if two else None, ptr(hidden), n, ptr(bound), ptr(w1t_hi), ptr(w1t_lo),
+                                     ptr(w0t_hi), ptr(w0t_lo), ptr(w_head), ctx.beta, colsum,
+                                     float(w_head.abs().max()), ptr(dz1), ptr(dz0), ptr(dx), k0, _lib.current_stream())
+            _lib.check(rc, "na_sdf_mlp_bwd")
+            # weight gradients: reductions over the rows (TF32 is what the reference itself runs its GEMMs in,
+            # imaginaire/trainers/base.py:172-175)
+            prev = torch.backends.cuda.matmul.allow_tf32
+            torch.backends.cuda.matmul.allow_tf32 = True
+            try:
+                dw0 = dz0.t() @ rows
+                db0 = dz0.sum(dim=0)
+                dw1 = dz1.t() @ hidden if two else None
+                db1 = dz1.sum(dim=0) if two else None
+                dwh = (d_sdf[None, :] @ hidden)
+                dbh = d_sdf.sum().reshape(1)
+            finally:
+                torch.backends.cuda.matmul.allow_tf32 = prev
+        return dx, dw0, db0, dw1, db1, dwh, dbh, None, None
+
+
+def fused_sdf_mlp(mlp, rows, beta, with_sdf=True, with_feat=True):
+    """Autograd-aware fused evaluation of an MLPforNeuralSDF (one hidden layer) on rows [M,K0]."""
+    l0, l1 = mlp.linears
+    sdf, feat = FusedSdfMlpFunction.apply(rows, l0.effective_weight(), l0.bias, l1.effective_weight(), l1.bias,
+                                          mlp.linear_sdf.weight, mlp.linear_sdf.bias, beta, with_feat)
+    return (sdf if with_sdf else None), (feat if with_feat else None)

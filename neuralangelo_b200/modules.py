@@ -137,13 +137,17 @@ class NeuralSDF(torch.nn.Module):
     def run_mlp(self, rows, with_sdf=True, with_feat=True):
         """rows [...,3+LD] -> [sdf [...,1] | None, feat [...,K] | None]."""
         needs_graph = torch.is_grad_enabled() and (rows.requires_grad or any(p.requires_grad for p in self.mlp.parameters()))
-        packed = None if needs_graph or not rows.is_cuda else self._packed_mlp()
+        packed = self._packed_mlp() if rows.is_cuda else None
         if packed is None:
             return self.mlp(rows, with_sdf=with_sdf, with_feat=with_feat)
         flat = rows.reshape(-1, rows.shape[-1])
         if flat.stride(-1) != 1 or flat.dtype != torch.float32:
             flat = flat.float().contiguous()
-        sdf, feat = packed.forward(flat, with_sdf=with_sdf, with_feat=with_feat)
+        if needs_graph:   # tcgen05 forward + input-gradient chain, weight gradients through torch (fused_mlp.py)
+            from .fused_mlp import fused_sdf_mlp
+            sdf, feat = fused_sdf_mlp(self.mlp, flat, packed.beta, with_sdf=with_sdf, with_feat=with_feat)
+        else:
+            sdf, feat = packed.forward(flat, with_sdf=with_sdf, with_feat=with_feat)
         lead = rows.shape[:-1]
         return [sdf.view(*lead, 1) if sdf is not None else None, feat.view(*lead, -1) if feat is not None else None]
 

@@ -64,3 +64,49 @@ def test_finite_difference_gradient_quality(na_lib, cuda_device):
     fd = (packed.forward(xp, with_feat=False)[0] - packed.forward(xm, with_feat=False)[0]) / (2 * eps)
     err = (fd.cpu().double() - ref).abs().max().item()
     assert err <= 2e-3 * max(ref.abs().max().item(), 1.0), err
+
+
+@pytest.mark.parametrize("with_feat,m", [(True, 700), (False, 1300)])
+def test_fused_sdf_mlp_backward(na_lib, cuda_device, with_feat, m):
+    """Gradients w.r.t. the input rows and every parameter (through weight norm) vs float64 autograd.
+    Upstream gradients span 1e-9 .. 1e-3 per row (what a mean-reduced loss produces) to exercise the row scaling."""
+    from neuralangelo_b200.fused_mlp import fused_sdf_mlp
+    k0, n = 131, 256
+    mlp = _mlp(k0, n, seed=11)
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(m, k0, generator=g) * 0.3
+    mag = 10.0 ** (-9 + 6 * torch.rand(m, 1, generator=g))
+    d_sdf = torch.randn(m, 1, generator=g) * mag
+    d_feat = torch.randn(m, n, generator=g) * mag * 0.1
+    d_sdf[5] = 0.0
+    d_feat[5] = 0.0                                      # an all-zero row
+    # float64 reference
+    md = mlp.double()
+    xd = x.double().requires_grad_(True)
+    s, f = md(xd, with_sdf=True, with_feat=with_feat)
+    loss = (s * d_sdf.double()).sum() + ((f * d_feat.double()).sum() if with_feat else 0.0)
+    loss.backward()
+    ref = {k: p.grad.clone() for k, p in md.named_parameters() if p.grad is not None}
+    ref_dx = xd.grad.clone()
+    # fused
+    mlp = mlp.float().to(cuda_device)
+    for p in mlp.parameters():
+        p.grad = None
+    buf = torch.zeros(m, k0 + 1, device=cuda_device)
+    buf[:, 1:] = x.to(cuda_device)
+    rows = buf[:, 1:].requires_grad_(True)
+    s, f = fused_sdf_mlp(mlp, rows, 100.0, with_sdf=True, with_feat=with_feat)
+    loss = (s * d_sdf.to(cuda_device)).sum() + ((f * d_feat.to(cuda_device)).sum() if with_feat else 0.0)
+    loss.backward()
+    gx = rows.grad if rows.grad is not None else buf.grad[:, 1:]
+    # per-row relative error of dx (rows differ by 6 orders of magnitude)
+    err = (gx.cpu().double() - ref_dx).abs().amax(dim=1)
+    scale = ref_dx.abs().amax(dim=1) + 1e-30
+    assert (err / scale).max().item() <= 1e-4, (err / scale).max().item()
+    for k, p in mlp.named_parameters():
+        if k not in ref:
+            assert p.grad is None or p.grad.abs().max().item() == 0, k
+            continue
+        r = ref[k]
+        rel = (p.grad.cpu().double() - r).norm().item() / max(r.norm().item(), 1e-30)
+        assert rel <= 2e-3, (k, rel)       # TF32 weight-gradient GEMMs

@@ -108,7 +108,8 @@ def test_no_grad_sdf_uses_fused_mlp_and_matches_autograd_path(na_lib, cuda_devic
     G = _load(golden_dir, 6)
     model = _build(G, 6, cuda_device)
     pts = (torch.rand(2, 50, 7, 3, generator=torch.Generator().manual_seed(0)) * 2 - 1).to(cuda_device)
-    sdf_graph, feat_graph = model.neural_sdf(pts)                 # autograd path (torch ops)
+    rows = model.neural_sdf.encode(pts)
+    sdf_graph, feat_graph = model.neural_sdf.mlp(rows)           # plain torch ops (cuBLAS fp32)
     with torch.no_grad():
         sdf_fused, feat_fused = model.neural_sdf(pts)            # fused kernel
         assert model.neural_sdf._packed is not None
