@@ -312,7 +312,7 @@ def extra_train_step(rank, world, dev, steps=30, warmup=8, taps=4, force_all_lev
     cfg = default_model_config()
     cfg.object.sdf.gradient.taps = taps
     model = Model(cfg, default_data_config()).to(dev)
-    ts = TrainStep(model, max_iter=500000, warm_up_end=5000)
+    ts = TrainStep(model, max_iter=500000, warm_up_end=5000, use_cuda_graph=True)
     if force_all_levels:
         ts.current_iteration = 5000 + 16 * 5000
     g = torch.Generator().manual_seed(1000 + rank)

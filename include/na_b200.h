@@ -233,7 +233,8 @@ int na_scale_inplace(float* params, int64_t n, float factor, void* stream);
  * ---------------------------------------------------------------------------------------- */
 int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, int n, int n_layers, const void* w0_hi,
                    const void* w0_lo, const float* b0, int k0_pad, const void* w1_hi, const void* w1_lo,
-                   const float* b1, const float* w_head, float b_head, float beta, float* sdf_out, float* feat_out,
+                   const float* b1, const float* w_head, const float* b_head /* device scalar */, float beta, float* sdf_out,
+                   float* feat_out,
                    int64_t ld_feat, float* hidden_out, int64_t ld_hidden, void* stream);
 
 /* Backward of na_sdf_mlp_fwd with respect to the input rows, plus the pre-activation gradients from which
@@ -242,13 +243,13 @@ int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, int n, int n_
  * two_layer = 0 is the SDF-only form (finite-difference taps): dz0 = d_sdf w_head * s'(z0), dx = dz0 W0.
  * hidden / feat are the activations saved by the forward ([m,n], stride ld_act); row_bound[m] >= max_j |d_feat[r,j]|
  * (used to scale each row into fp16 range); w1t / w0t are W1^T and W0^T (rows zero-padded to k0_pad) packed
- * like the forward weights; w1_colsum_max = max_j sum_k |W1[k,j]|, w_head_absmax = max |w_head|.
+ * like the forward weights; norms = DEVICE float[2] {max_j sum_k |W1[k,j]|, max |w_head|} (scaling bounds).
  * Replaces: the autograd backward of MLPforNeuralSDF.forward (projects/neuralangelo/utils/mlp.py:55-69). */
 int na_sdf_mlp_bwd(int64_t m, int n, int k0, int k0_pad, int two_layer, const float* d_sdf, const float* d_feat,
                    const float* feat, const float* hidden, int64_t ld_act, const float* row_bound,
                    const void* w1t_hi, const void* w1t_lo, const void* w0t_hi, const void* w0t_lo,
-                   const float* w_head, float beta, float w1_colsum_max, float w_head_absmax, float* dz1, float* dz0,
-                   float* dx, int64_t ld_dx, void* stream);
+                   const float* w_head, float beta, const float* norms, float* dz1, float* dz0, float* dx,
+                   int64_t ld_dx, void* stream);
 
 #ifdef __cplusplus
 }

@@ -79,9 +79,9 @@ def _declare(lib):
         "na_adamw_step": (ctypes.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, f32, ctypes.c_int, vp]),
         "na_scale_inplace": (ctypes.c_int, [vp, i64, f32, vp]),
         "na_sdf_mlp_fwd": (ctypes.c_int, [vp, i64, i64, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, vp, ctypes.c_int,
-                                          vp, vp, vp, vp, f32, f32, vp, vp, i64, vp, i64, vp]),
+                                          vp, vp, vp, vp, vp, f32, vp, vp, i64, vp, i64, vp]),
         "na_sdf_mlp_bwd": (ctypes.c_int, [i64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, vp, vp, i64, vp,
-                                          vp, vp, vp, vp, vp, f32, f32, f32, vp, vp, vp, i64, vp]),
+                                          vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, i64, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

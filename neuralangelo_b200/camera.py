@@ -11,13 +11,29 @@ def _pose_invert(pose):
     return torch.cat([R_inv, -R_inv @ t], dim=-1)
 
 
+def _inv3x3(m):
+    """Closed-form inverse of [...,3,3] matrices (adjugate / determinant).  `torch.inverse` goes through a
+    LAPACK-style factorisation with a host-side status check, which stalls the stream every step and cannot be
+    captured in a CUDA graph."""
+    a, b, c = m[..., 0, 0], m[..., 0, 1], m[..., 0, 2]
+    d, e, f = m[..., 1, 0], m[..., 1, 1], m[..., 1, 2]
+    g, h, i = m[..., 2, 0], m[..., 2, 1], m[..., 2, 2]
+    A, B, C = e * i - f * h, c * h - b * i, b * f - c * e
+    D, E, F = f * g - d * i, a * i - c * g, c * d - a * f
+    G, H, I = d * h - e * g, b * g - a * h, a * e - b * d
+    det = a * A + b * D + c * G
+    adj = torch.stack([torch.stack([A, B, C], dim=-1), torch.stack([D, E, F], dim=-1), torch.stack([G, H, I], dim=-1)],
+                      dim=-2)
+    return adj / det[..., None, None]
+
+
 def _to_hom(X):
     return torch.cat([X, torch.ones_like(X[..., :1])], dim=-1)
 
 
 def _rays_from_pixels(xy, pose, intr):
     """xy [B,R,2] pixel centres -> (center [B,R,3], ray [B,R,3] at depth 1), camera.py:300-311."""
-    grid_3D = _to_hom(xy) @ intr.inverse().transpose(-1, -2)            # img2cam
+    grid_3D = _to_hom(xy) @ _inv3x3(intr).transpose(-1, -2)             # img2cam
     pose_inv = _pose_invert(pose)
     center_3D = _to_hom(torch.zeros_like(grid_3D)) @ pose_inv.transpose(-1, -2)   # cam2world of the origin
     grid_3D = _to_hom(grid_3D) @ pose_inv.transpose(-1, -2)

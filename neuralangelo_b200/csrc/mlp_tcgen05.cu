@@ -60,7 +60,7 @@ struct MlpParams {
     int n_layers;         // 1 (SDF only) or 2 (SDF + feature)
     Layer layer[2];
     const float* w_head;  // [N] SDF head weights (applied to layer 0's activations) or null
-    float b_head;
+    const float* b_head;  // device scalar
     float beta;           // softplus beta
     float* sdf_out;       // [M] or null
     float* feat_out;      // [M, N] rows, stride ld_feat, or null
@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
                     head_partial[half * kTileM + row] = dot;
                     asm volatile("bar.sync 1, %0;" ::"n"(kComputeThreads) : "memory");
                     if (half == 0 && row0 + row < P.m && P.sdf_out)
-                        P.sdf_out[row0 + row] = head_partial[row] + head_partial[kTileM + row] + P.b_head;
+                        P.sdf_out[row0 + row] = head_partial[row] + head_partial[kTileM + row] + __ldg(P.b_head);
                     asm volatile("bar.sync 1, %0;" ::"n"(kComputeThreads) : "memory");
                 }
                 tc_fence_before();
@@ -427,8 +427,7 @@ struct BwdParams {
     Layer w0t;             // packed W0^T: B[col][k_hidden] with col padded to k0_pad; k_pad = n
     const float* w_head;   // [N]
     float beta;
-    float w1_colsum_max;   // max_j sum_k |W1[k,j]|   (bound of |dz1 W1| per unit |dz1|)
-    float w_head_absmax;
+    const float* norms;    // device [2]: max_j sum_k |W1[k,j]| (bound of |dz1 W1| per unit |dz1|), max |w_head|
     float* dz1;            // [M,N] out (two_layer), stride ld_act
     float* dz0;            // [M,N] out, stride ld_act
     float* dx;             // [M,k0] out, stride ld_dx
@@ -555,6 +554,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_c
         const int row = quarter * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
         const float beta = P.beta;
+        const float w1_colsum_max = __ldg(P.norms), w_head_absmax = __ldg(P.norms + 1);
         uint32_t mma_it = 0;
         // write 32 consecutive values of this thread's row (scaled) as four fp16 hi/lo chunks of the A operand
         auto store_a = [&](const float (&v)[32], int c0, float scale) {
@@ -582,7 +582,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_c
             if (P.two_layer) {
                 const float b1 = valid ? __ldg(P.row_bound + grow) : 0.f;
                 scale_a = pow2_scale(b1);
-                scale_b = pow2_scale(b1 * P.w1_colsum_max + fabsf(dsdf) * P.w_head_absmax);
+                scale_b = pow2_scale(b1 * w1_colsum_max + fabsf(dsdf) * w_head_absmax);
                 // ---- prologue: dz1 = d_feat * s'(z1) -> HBM (fp32) and A operand (scaled, split)
                 for (int c0 = col_begin; c0 < col_end; c0 += 32) {
                     float v[32];
@@ -603,7 +603,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_c
                 }
             } else {
                 scale_a = 1.f;
-                scale_b = pow2_scale(fabsf(dsdf) * P.w_head_absmax);
+                scale_b = pow2_scale(fabsf(dsdf) * w_head_absmax);
                 // ---- prologue (SDF-only rows): dz0 = d_sdf w_head * s'(z0)
                 for (int c0 = col_begin; c0 < col_end; c0 += 32) {
                     float v[32];
@@ -694,17 +694,33 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_c
     }
 }
 
+// The opt-in to > 48 KB of dynamic shared memory is per device and is not a stream operation: do it once per
+// (kernel, device) so that later launches -- possibly under CUDA-graph capture -- make no attribute call.
+int ensure_smem_attr(int which, const void* func, const char* what) {
+    static bool done[2][64] = {};
+    int dev = 0;
+    if (int rc = na::check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return rc;
+    if (dev < 0 || dev >= 64 || !done[which][dev]) {
+        if (int rc = na::check_cuda(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes),
+                                    what))
+            return rc;
+        if (dev >= 0 && dev < 64) done[which][dev] = true;
+    }
+    return NA_OK;
+}
+
 }  // namespace
 
 extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, int n, int n_layers,
                               const void* w0_hi, const void* w0_lo, const float* b0, int k0_pad, const void* w1_hi,
-                              const void* w1_lo, const float* b1, const float* w_head, float b_head, float beta,
+                              const void* w1_lo, const float* b1, const float* w_head, const float* b_head, float beta,
                               float* sdf_out, float* feat_out, int64_t ld_feat, float* hidden_out, int64_t ld_hidden,
                               void* stream) {
     na::clear_error();
     NA_REQUIRE(m >= 0, "sdf_mlp_fwd: negative row count");
     if (m == 0) return NA_OK;
     NA_REQUIRE(x && w0_hi && w0_lo && b0, "sdf_mlp_fwd: null pointer");
+    NA_REQUIRE(!w_head || b_head, "sdf_mlp_fwd: w_head given without b_head");
     NA_REQUIRE(n % 64 == 0 && n >= 64 && n <= kMaxN, "sdf_mlp_fwd: hidden width %d unsupported (64, 128, 192, 256)", n);
     NA_REQUIRE(k0 >= 1 && k0 <= k0_pad && k0_pad % 16 == 0 && k0_pad <= kMaxK,
                "sdf_mlp_fwd: k0=%d k0_pad=%d unsupported (k0_pad multiple of 16, <= %d)", k0, k0_pad, kMaxK);
@@ -722,10 +738,7 @@ extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, in
     P.layer[1] = Layer{(const __half*)w1_hi, (const __half*)w1_lo, b1, n};
     P.w_head = w_head, P.b_head = b_head, P.beta = beta;
     P.sdf_out = sdf_out, P.feat_out = feat_out, P.ld_feat = ld_feat, P.hidden_out = hidden_out, P.ld_hidden = ld_hidden;
-    if (int rc = na::check_cuda(cudaFuncSetAttribute(sdf_mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                     kSmemBytes),
-                                "cudaFuncSetAttribute(sdf_mlp_fwd_kernel)"))
-        return rc;
+    if (int rc = ensure_smem_attr(0, (const void*)sdf_mlp_fwd_kernel, "cudaFuncSetAttribute(sdf_mlp_fwd_kernel)")) return rc;
     const int64_t tiles = (m + kTileM - 1) / kTileM;
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
     sdf_mlp_fwd_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);
@@ -736,15 +749,15 @@ extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, in
 extern "C" int na_sdf_mlp_bwd(int64_t m, int n, int k0, int k0_pad, int two_layer, const float* d_sdf,
                               const float* d_feat, const float* feat, const float* hidden, int64_t ld_act,
                               const float* row_bound, const void* w1t_hi, const void* w1t_lo, const void* w0t_hi,
-                              const void* w0t_lo, const float* w_head, float beta, float w1_colsum_max,
-                              float w_head_absmax, float* dz1, float* dz0, float* dx, int64_t ld_dx, void* stream) {
+                              const void* w0t_lo, const float* w_head, float beta, const float* norms,
+                              float* dz1, float* dz0, float* dx, int64_t ld_dx, void* stream) {
     na::clear_error();
     NA_REQUIRE(m >= 0, "sdf_mlp_bwd: negative row count");
     if (m == 0) return NA_OK;
     NA_REQUIRE(n % 64 == 0 && n >= 64 && n <= kMaxN, "sdf_mlp_bwd: hidden width %d unsupported", n);
     NA_REQUIRE(k0 >= 1 && k0 <= k0_pad && k0_pad % 16 == 0 && k0_pad <= kMaxK, "sdf_mlp_bwd: k0=%d k0_pad=%d unsupported",
                k0, k0_pad);
-    NA_REQUIRE(hidden && w0t_hi && w0t_lo && w_head && dz0 && dx, "sdf_mlp_bwd: null pointer");
+    NA_REQUIRE(hidden && w0t_hi && w0t_lo && w_head && norms && dz0 && dx, "sdf_mlp_bwd: null pointer");
     NA_REQUIRE(!two_layer || (d_feat && feat && row_bound && w1t_hi && w1t_lo && dz1),
                "sdf_mlp_bwd: the two-layer form needs d_feat, feat, row_bound, W1^T and dz1");
     NA_REQUIRE(ld_act % 4 == 0 && ((uintptr_t)hidden | (uintptr_t)dz0 | (uintptr_t)dz1 | (uintptr_t)d_feat |
@@ -755,12 +768,9 @@ extern "C" int na_sdf_mlp_bwd(int64_t m, int n, int k0, int k0_pad, int two_laye
     P.d_sdf = d_sdf, P.d_feat = d_feat, P.feat = feat, P.hidden = hidden, P.ld_act = ld_act, P.row_bound = row_bound;
     P.w1t = Layer{(const __half*)w1t_hi, (const __half*)w1t_lo, nullptr, n};
     P.w0t = Layer{(const __half*)w0t_hi, (const __half*)w0t_lo, nullptr, n};
-    P.w_head = w_head, P.beta = beta, P.w1_colsum_max = w1_colsum_max, P.w_head_absmax = w_head_absmax;
+    P.w_head = w_head, P.beta = beta, P.norms = norms;
     P.dz1 = dz1, P.dz0 = dz0, P.dx = dx, P.ld_dx = ld_dx;
-    if (int rc = na::check_cuda(cudaFuncSetAttribute(sdf_mlp_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                     kSmemBytes),
-                                "cudaFuncSetAttribute(sdf_mlp_bwd_kernel)"))
-        return rc;
+    if (int rc = ensure_smem_attr(1, (const void*)sdf_mlp_bwd_kernel, "cudaFuncSetAttribute(sdf_mlp_bwd_kernel)")) return rc;
     const int64_t tiles = (m + kTileM - 1) / kTileM;
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
     sdf_mlp_bwd_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);

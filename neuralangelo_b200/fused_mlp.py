@@ -54,7 +54,7 @@ class PackedSdfMlp:
             self.b0 = l0.bias.detach().float().contiguous()
             self.b1 = l1.bias.detach().float().contiguous()
             self.w_head = mlp.linear_sdf.weight.detach().float().reshape(-1).contiguous()
-            self.b_head = float(mlp.linear_sdf.bias.detach().float().item())
+            self.b_head = mlp.linear_sdf.bias.detach().float().reshape(1).clone()
 
     def forward(self, rows, with_sdf=True, with_feat=True, with_hidden=False):
         """rows: [M, K0] fp32 CUDA tensor, unit stride in the last dim (row stride free).
@@ -69,7 +69,7 @@ class PackedSdfMlp:
         rc = _L().na_sdf_mlp_fwd(ptr(rows), rows.stride(0), m, self.k0, self.n, 2 if with_feat else 1,
                                  ptr(self.w0_hi), ptr(self.w0_lo), ptr(self.b0), self.k0_pad,
                                  ptr(self.w1_hi), ptr(self.w1_lo), ptr(self.b1),
-                                 ptr(self.w_head) if with_sdf else None, self.b_head, self.beta,
+                                 ptr(self.w_head) if with_sdf else None, ptr(self.b_head), self.beta,
                                  ptr(sdf), ptr(feat), self.n, ptr(hidden), self.n, _lib.current_stream())
         _lib.check(rc, "na_sdf_mlp_fwd")
         return (sdf, feat, hidden) if with_hidden else (sdf, feat)
@@ -95,8 +95,8 @@ class FusedSdfMlpFunction(torch.autograd.Function):
         b0c, b1c, whc = b0.detach().float().contiguous(), b1.detach().float().contiguous(), \
             w_head.detach().float().reshape(-1).contiguous()
         rc = _L().na_sdf_mlp_fwd(ptr(rows), rows.stride(0), m, k0, n, 2 if with_feat else 1, ptr(w0_hi), ptr(w0_lo),
-                                 ptr(b0c), k0_pad, ptr(w1_hi), ptr(w1_lo), ptr(b1c), ptr(whc), float(b_head.detach()),
-                                 float(beta), ptr(sdf), ptr(feat), n, ptr(hidden), n, _lib.current_stream())
+                                 ptr(b0c), k0_pad, ptr(w1_hi), ptr(w1_lo), ptr(b1c), ptr(whc),
+                                 ptr(b_head.detach().float().reshape(1).contiguous()), float(beta), ptr(sdf), ptr(feat), n, ptr(hidden), n, _lib.current_stream())
         _lib.check(rc, "na_sdf_mlp_fwd")
         ctx.save_for_backward(rows, hidden, feat if with_feat else hidden, w0, w1, whc)
         ctx.beta, ctx.with_feat = float(beta), with_feat
@@ -122,17 +122,18 @@ class FusedSdfMlpFunction(torch.autograd.Function):
                 d_feat = d_feat.float().contiguous()
                 w1t_hi, w1t_lo = pack_weight(w1.detach().float().t().contiguous(), n)
                 bound = d_feat.abs().amax(dim=1).contiguous()
-                colsum = float(w1.detach().abs().sum(dim=0).max())
+                colsum = w1.detach().abs().sum(dim=0).max().reshape(1)
                 dz1 = torch.empty(m, n, dtype=torch.float32, device=dev)
             else:
                 w1t_hi = w1t_lo = bound = dz1 = None
-                colsum = 0.0
+                colsum = torch.zeros(1, device=dev)
+            norms = torch.cat([colsum.float(), w_head.abs().max().reshape(1)])   # device scalars: no host sync
             dz0 = torch.empty(m, n, dtype=torch.float32, device=dev)
             dx = torch.empty(m, k0, dtype=torch.float32, device=dev)
             rc = _L().na_sdf_mlp_bwd(m, n, k0, k0_pad, 1 if two else 0, ptr(d_sdf), ptr(d_feat) if two else None,
                                      ptr(feat) if two else None, ptr(hidden), n, ptr(bound), ptr(w1t_hi), ptr(w1t_lo),
-                                     ptr(w0t_hi), ptr(w0t_lo), ptr(w_head), ctx.beta, colsum,
-                                     float(w_head.abs().max()), ptr(dz1), ptr(dz0), ptr(dx), k0, _lib.current_stream())
+                                     ptr(w0t_hi), ptr(w0t_lo), ptr(w_head), ctx.beta, ptr(norms), ptr(dz1), ptr(dz0),
+                                     ptr(dx), k0, _lib.current_stream())
             _lib.check(rc, "na_sdf_mlp_bwd")
             # weight gradients: reductions over the rows (TF32 is what the reference itself runs its GEMMs in,
             # imaginaire/trainers/base.py:172-175)

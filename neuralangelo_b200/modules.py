@@ -28,6 +28,17 @@ def positional_encoding(input, num_freq_bases):
     return enc.view(*input.shape[:-1], -1)
 
 
+_tap_cache = {}
+
+
+def _tap_tensor(taps, device):
+    """Device copy of a tap-offset tuple, cached (a fresh torch.tensor() per call is a pageable H2D copy)."""
+    key = (taps, str(device))
+    if key not in _tap_cache:
+        _tap_cache[key] = torch.tensor(taps, dtype=torch.float32, device=device)
+    return _tap_cache[key]
+
+
 class _EncodeRows(torch.autograd.Function):
     """[T,N,3+L*F] rows = (x + tap_t) ++ hash-grid features of (x + tap_t); gradient to the table only."""
 
@@ -38,7 +49,7 @@ class _EncodeRows(torch.autograd.Function):
         # rows padded to 3+width+1 floats with the pad in FRONT: features start 16 bytes into the row, so the
         # kernel's 16-byte vector stores apply; the returned view drops the pad column.
         buf = torch.empty(n_taps, n, width + 4, dtype=torch.float32, device=pts.device)
-        offs = torch.tensor(taps, dtype=torch.float32, device=pts.device)
+        offs = _tap_tensor(taps, pts.device)
         buf[:, :, 1:4] = pts[None, :, :] + offs[:, None, :]
         hashgrid.encode_taps(module.desc, table, pts, unit_map, active_levels, taps, out=buf[:, :, 4:])
         ctx.save_for_backward(pts)
@@ -213,7 +224,7 @@ class NeuralSDF(torch.nn.Module):
                 hessian = torch.cat([(s[0] + s[1] - 2 * sdf) / (eps ** 2), (s[2] + s[3] - 2 * sdf) / (eps ** 2),
                                      (s[4] + s[5] - 2 * sdf) / (eps ** 2)], dim=-1)
         else:
-            k = [torch.tensor(v, dtype=x.dtype, device=x.device) for v in ((1, -1, -1), (-1, -1, 1), (-1, 1, -1), (1, 1, 1))]
+            k = _tap_tensor(((1., -1., -1.), (-1., -1., 1.), (-1., 1., -1.), (1., 1., 1.)), x.device).to(x.dtype)
             gradient = (k[0] * s[0] + k[1] * s[1] + k[2] * s[2] + k[3] * s[3]) / (4.0 * eps)
             if training:
                 assert sdf is not None

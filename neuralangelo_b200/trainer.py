@@ -14,8 +14,13 @@ from .optim import FusedAdamW
 
 class TrainStep:
     def __init__(self, model, cfg=None, lr=1e-3, weight_decay=1e-2, max_iter=500000, warm_up_end=5000,
-                 loss_weights=None, two_steps=(300000, 400000), gamma=10.0):
+                 loss_weights=None, two_steps=(300000, 400000), gamma=10.0, use_cuda_graph=False, allow_tf32=True):
         self.model = model
+        # imaginaire/trainers/base.py:169-178 (init_amp): TF32 library GEMMs are allowed by default.  Here that
+        # only concerns the colour / background MLPs and the weight-gradient reductions; the SDF network, whose
+        # finite differences need fp32-grade products, runs in the split-precision tcgen05 kernels regardless.
+        torch.backends.cudnn.allow_tf32 = allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = allow_tf32
         self.max_iter, self.warm_up_end = max_iter, warm_up_end
         self.two_steps, self.gamma = two_steps, gamma
         self.base_lr = lr
@@ -31,6 +36,13 @@ class TrainStep:
         self.optim = FusedAdamW(model, lr=lr, weight_decay=weight_decay)
         self.current_iteration = 0
         self.losses, self.metrics = {}, {}
+        # CUDA-graph mode: forward + loss + backward are captured once per schedule state and replayed; the
+        # per-iteration scalars that torch ops consume (loss weights) live in a device tensor.
+        self.use_cuda_graph = use_cuda_graph
+        self._graph = self._graph_key = self._static = self._static_loss = None
+        dev = next(model.parameters()).device
+        self._w_dev = torch.zeros(3, dtype=torch.float32, device=dev)
+        self._w_host = torch.zeros(3, dtype=torch.float32).pin_memory() if dev.type == "cuda" else torch.zeros(3)
 
     def lr_factor(self, it):
         """two_steps_with_warmup, misc.py:38-52."""
@@ -61,26 +73,74 @@ class TrainStep:
 
     def compute_loss(self, out, image_sampled):
         """trainer.py:40-48 (train mode)."""
-        self.losses["render"] = torch_F.l1_loss(out["rgb"], image_sampled) * 3
-        self.metrics["psnr"] = -10 * torch_F.mse_loss(out["rgb"], image_sampled).log10()
-        total = self.weights["render"] * self.losses["render"]
+        # (self.losses / self.metrics keep DETACHED values: a live reference to the autograd graph would pin its
+        #  AccumulateGrad nodes to the stream of this iteration and break CUDA-graph capture of a later one)
+        render = torch_F.l1_loss(out["rgb"], image_sampled) * 3
+        self.losses["render"] = render.detach()
+        self.metrics["psnr"] = (-10 * torch_F.mse_loss(out["rgb"].detach(), image_sampled).log10())
+        w = self._w_dev   # device copies of self.weights (refreshed every iteration by _upload_weights)
+        total = w[0] * render
         if "eikonal" in self.weights:
-            self.losses["eikonal"] = eikonal_loss(out["gradients"], outside=out["outside"])
-            total = total + self.weights["eikonal"] * self.losses["eikonal"]
+            eik = eikonal_loss(out["gradients"], outside=out["outside"])
+            self.losses["eikonal"] = eik.detach()
+            total = total + w[1] * eik
         if "curvature" in self.weights:
-            self.losses["curvature"] = curvature_loss(out["hessians"], outside=out["outside"])
-            total = total + self.weights["curvature"] * self.losses["curvature"]
+            curv = curvature_loss(out["hessians"], outside=out["outside"])
+            self.losses["curvature"] = curv.detach()
+            total = total + w[2] * curv
         return total
+
+    def _upload_weights(self):
+        self._w_host[0] = self.weights["render"]
+        self._w_host[1] = self.weights.get("eikonal", 0.0)
+        self._w_host[2] = self.weights.get("curvature", 0.0)
+        self._w_dev.copy_(self._w_host, non_blocking=True)
+
+    def _forward_backward(self, data):
+        out = self.model(data)
+        loss = self.compute_loss(out, data["image_sampled"])
+        loss.backward()
+        return loss
+
+    def _schedule_key(self, data):
+        """Everything that is baked into kernel arguments at capture time."""
+        m = self.model
+        sdf = m.neural_sdf
+        ratio = min(m.progress / m.anneal_end, 1.0)
+        return (getattr(sdf, "active_levels", None), getattr(sdf, "normal_eps", None), ratio, m.training,
+                tuple((k, tuple(v.shape), v.dtype) for k, v in sorted(data.items())))
+
+    def _graphed_forward_backward(self, data):
+        key = self._schedule_key(data)
+        if self._graph is None or key != self._graph_key:
+            self._static = {k: v.clone() for k, v in data.items()}
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):          # warm-up outside capture (cuBLAS workspaces, lazy inits)
+                for _ in range(2):
+                    self._forward_backward(self._static)
+            torch.cuda.current_stream().wait_stream(side)
+            self.optim.zero_grad()
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph, stream=side):   # same stream as the warm-up (AccumulateGrad streams)
+                self._static_loss = self._forward_backward(self._static)
+            self._graph_key = key
+        for k, v in data.items():
+            self._static[k].copy_(v, non_blocking=True)
+        self._graph.replay()
+        return self._static_loss
 
     def step(self, data):
         """One iteration on this rank's batch: data = dict(pose, intr, idx, ray_idx, image_sampled)."""
         it = self.current_iteration
         self.start_of_iteration(it)
         self.model.train()
-        out = self.model(data)
-        loss = self.compute_loss(out, data["image_sampled"])
-        loss.backward()
+        self._upload_weights()
+        if self.use_cuda_graph:
+            loss = self._graphed_forward_backward(data)
+        else:
+            loss = self._forward_backward(data)
         grad_scale = parallel.allreduce_gradients(*self.optim.grad_views())
         self.optim.step(grad_scale=grad_scale, lr=self.base_lr * self.lr_factor(it))
         self.current_iteration += 1
-        return loss.detach()
+        return loss

@@ -14,7 +14,7 @@ taps = int(os.environ.get("TAPS", "4"))
 cfg.object.sdf.gradient.taps = taps
 model = Model(cfg, default_data_config()).to(dev)
 force16 = os.environ.get("FORCE16", "1") == "1"
-ts = TrainStep(model, max_iter=500000, warm_up_end=5000)
+ts = TrainStep(model, max_iter=500000, warm_up_end=5000, use_cuda_graph=os.environ.get("GRAPH", "0") == "1")
 if force16:
     ts.current_iteration = 5000 + 16 * 5000   # all 16 levels active, eps = 1/2048
 

@@ -34,3 +34,15 @@ GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN_DIR
+
+
+@pytest.fixture(autouse=True)
+def _fp32_library_gemms():
+    """Parity tests compare against fp32/float64 references: keep library GEMMs in full fp32 unless a test opts in
+    (TrainStep enables TF32 by default, as the reference's trainer does)."""
+    import torch
+    prev = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    yield
+    torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = prev
