@@ -128,14 +128,15 @@ int na_density_alphas_fwd(const float* dens, const float* dists, const float* di
 int na_density_alphas_bwd(const float* dens, const float* dists, const float* dist_far, const float* d_alphas,
                           int64_t n_rays, int n_samples, float* d_dens, void* stream);
 
-/* NeuS opacity from SDF value + SDF gradient along the ray; anneal_ratio = min(progress/anneal_end, 1).
+/* NeuS opacity from SDF value + SDF gradient along the ray; anneal_ratio = DEVICE scalar holding
+ * min(progress/anneal_end, 1) (device-resident so that a captured CUDA graph follows the schedule).
  * Replaces: Model.compute_neus_alphas + _get_iter_cos, projects/neuralangelo/model.py:275-298. */
 int na_neus_alphas_fwd(const float* sdf, const float* grad, const float* dists, const float* ray_unit,
-                       const float* dist_far, const float* s_var, float anneal_ratio, int64_t n_rays,
+                       const float* dist_far, const float* s_var, const float* anneal_ratio, int64_t n_rays,
                        int n_samples, float* alphas, void* stream);
 /* d_s_var (device scalar) is accumulated atomically; d_sdf [R,N], d_grad [R,N,3] are overwritten. */
 int na_neus_alphas_bwd(const float* sdf, const float* grad, const float* dists, const float* ray_unit,
-                       const float* dist_far, const float* s_var, float anneal_ratio, const float* d_alphas,
+                       const float* dist_far, const float* s_var, const float* anneal_ratio, const float* d_alphas,
                        int64_t n_rays, int n_samples, float* d_sdf, float* d_grad, float* d_s_var, void* stream);
 
 /* Inverse-CDF sampling: bins [R,n_bins], weights [R,n_bins-1], unif [n_fine] (device; the u values,
@@ -159,12 +160,12 @@ int na_merge_sorted(const float* dists, const float* sdfs, const float* dists_fi
  * rgb [R,3]; weights [R,n_obj+n_bg] and opacity [R] optional (NULL).  n_bg may be 0 (no background).
  * n_obj + n_bg <= 512.  Replaces: model.py:132-141 with the alphas of :168-169 and :198. */
 int na_neus_render_fwd(const float* sdf, const float* grad, const float* dists_obj, const float* ray_unit,
-                       const float* dist_far, const float* s_var, float anneal_ratio, const float* rgb_obj,
+                       const float* dist_far, const float* s_var, const float* anneal_ratio, const float* rgb_obj,
                        int n_obj, const float* dens_bg, const float* dists_bg, const float* rgb_bg, int n_bg,
                        int64_t n_rays, float* rgb, float* weights, float* opacity, void* stream);
 /* d_weights optional (NULL).  Outputs overwritten except d_s_var (atomic accumulate). */
 int na_neus_render_bwd(const float* sdf, const float* grad, const float* dists_obj, const float* ray_unit,
-                       const float* dist_far, const float* s_var, float anneal_ratio, const float* rgb_obj,
+                       const float* dist_far, const float* s_var, const float* anneal_ratio, const float* rgb_obj,
                        int n_obj, const float* dens_bg, const float* dists_bg, const float* rgb_bg, int n_bg,
                        int64_t n_rays, const float* d_rgb, const float* d_weights, float* d_sdf, float* d_grad,
                        float* d_s_var, float* d_rgb_obj, float* d_dens_bg, float* d_rgb_bg, void* stream);

@@ -60,14 +60,14 @@ def _declare(lib):
         "na_composite_bwd": (ctypes.c_int, [vp, vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp, vp]),
         "na_density_alphas_fwd": (ctypes.c_int, [vp, vp, vp, i64, ctypes.c_int, vp, vp]),
         "na_density_alphas_bwd": (ctypes.c_int, [vp, vp, vp, vp, i64, ctypes.c_int, vp, vp]),
-        "na_neus_alphas_fwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, f32, i64, ctypes.c_int, vp, vp]),
-        "na_neus_alphas_bwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, f32, vp, i64, ctypes.c_int, vp, vp, vp, vp]),
+        "na_neus_alphas_fwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, i64, ctypes.c_int, vp, vp]),
+        "na_neus_alphas_bwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, i64, ctypes.c_int, vp, vp, vp, vp]),
         "na_sample_pdf": (ctypes.c_int, [vp, vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp]),
         "na_neus_upsample": (ctypes.c_int, [vp, vp, vp, f32, i64, ctypes.c_int, ctypes.c_int, vp, vp]),
         "na_merge_sorted": (ctypes.c_int, [vp, vp, vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp, vp]),
-        "na_neus_render_fwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, f32, vp, ctypes.c_int, vp, vp, vp, ctypes.c_int,
+        "na_neus_render_fwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, ctypes.c_int, vp, vp, vp, ctypes.c_int,
                                               i64, vp, vp, vp, vp]),
-        "na_neus_render_bwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, f32, vp, ctypes.c_int, vp, vp, vp, ctypes.c_int,
+        "na_neus_render_bwd": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, ctypes.c_int, vp, vp, vp, ctypes.c_int,
                                               i64, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
         "na_mc_scratch_bytes": (ctypes.c_int64, [ctypes.c_int, ctypes.c_int, ctypes.c_int]),
         "na_mc_count": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double, vp, i64, vp, vp]),

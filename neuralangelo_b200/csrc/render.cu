@@ -220,13 +220,15 @@ template <bool BWD>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 neus_alphas_kernel(const float* __restrict__ sdf, const float* __restrict__ grad, const float* __restrict__ dists,
                    const float* __restrict__ ray_unit, const float* __restrict__ dist_far,
-                   const float* __restrict__ s_var, float anneal_ratio, const float* __restrict__ d_alphas,
+                   const float* __restrict__ s_var, const float* __restrict__ anneal_ptr,
+                   const float* __restrict__ d_alphas,
                    int64_t n_rays, int n, float* __restrict__ alphas, float* __restrict__ d_sdf,
                    float* __restrict__ d_grad, float* __restrict__ d_s_var) {
     const int lane = threadIdx.x & 31;
     const int64_t ray = (int64_t)blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
     if (ray >= n_rays) return;
     const float inv_s = expf(__ldg(s_var));
+    const float anneal_ratio = __ldg(anneal_ptr);
     const float far = dist_far ? dist_far[ray] : 1e10f;
     const float r0 = ray_unit[ray * 3 + 0], r1 = ray_unit[ray * 3 + 1], r2 = ray_unit[ray * 3 + 2];
     const float* d = dists + ray * n;
@@ -384,7 +386,7 @@ merge_sorted_kernel(const float* __restrict__ dists, const float* __restrict__ s
 struct RenderArgs {
     const float *sdf, *grad, *dists_obj, *ray_unit, *dist_far, *s_var, *rgb_obj;  // object: [R,No(,3)]
     const float *dens_bg, *dists_bg, *rgb_bg;                                       // background: [R,Nb(,3)] or null
-    float anneal_ratio;
+    const float* anneal_ratio;  // device scalar: min(progress / anneal_end, 1)
     int n_obj, n_bg;
     int64_t n_rays;
 };
@@ -401,6 +403,7 @@ neus_render_kernel(const RenderArgs A, float* __restrict__ rgb_out, float* __res
     if (ray >= A.n_rays) return;
     const int n_obj = A.n_obj, n_bg = A.n_bg, n = n_obj + n_bg;
     const float inv_s = expf(__ldg(A.s_var));
+    const float anneal = __ldg(A.anneal_ratio);
     const float far = A.dist_far ? A.dist_far[ray] : 1e10f;
     const float r0 = A.ray_unit[ray * 3 + 0], r1 = A.ray_unit[ray * 3 + 1], r2 = A.ray_unit[ray * 3 + 2];
     const float* dob = A.dists_obj + ray * n_obj;
@@ -418,7 +421,7 @@ neus_render_kernel(const RenderArgs A, float* __restrict__ rgb_out, float* __res
         if (i < n_obj) {
             const int64_t s = ray * n_obj + i;
             const float tc = r0 * A.grad[s * 3 + 0] + r1 * A.grad[s * 3 + 1] + r2 * A.grad[s * 3 + 2];
-            const NeusAlpha na_ = neus_alpha<BWD>(A.sdf[s], tc, interval(dob, i, n_obj, far), inv_s, A.anneal_ratio);
+            const NeusAlpha na_ = neus_alpha<BWD>(A.sdf[s], tc, interval(dob, i, n_obj, far), inv_s, anneal);
             al = na_.alpha;
             gsdf[c] = na_.d_sdf, gcos[c] = na_.d_cos, ginv[c] = na_.d_invs;
         } else if (i < n) {
@@ -560,10 +563,10 @@ extern "C" int na_density_alphas_bwd(const float* dens, const float* dists, cons
 }
 
 extern "C" int na_neus_alphas_fwd(const float* sdf, const float* grad, const float* dists, const float* ray_unit,
-                                  const float* dist_far, const float* s_var, float anneal_ratio, int64_t n_rays,
+                                  const float* dist_far, const float* s_var, const float* anneal_ratio, int64_t n_rays,
                                   int n_samples, float* alphas, void* stream) {
     NA_RAYS_PROLOGUE("neus_alphas_fwd", n_samples)
-    NA_REQUIRE(sdf && grad && dists && ray_unit && s_var && alphas, "neus_alphas_fwd: null pointer");
+    NA_REQUIRE(sdf && grad && dists && ray_unit && s_var && anneal_ratio && alphas, "neus_alphas_fwd: null pointer");
     neus_alphas_kernel<false><<<ray_blocks(n_rays), kWarpsPerCta * 32, 0, s>>>(
         sdf, grad, dists, ray_unit, dist_far, s_var, anneal_ratio, nullptr, n_rays, n_samples, alphas, nullptr,
         nullptr, nullptr);
@@ -572,11 +575,11 @@ extern "C" int na_neus_alphas_fwd(const float* sdf, const float* grad, const flo
 }
 
 extern "C" int na_neus_alphas_bwd(const float* sdf, const float* grad, const float* dists, const float* ray_unit,
-                                  const float* dist_far, const float* s_var, float anneal_ratio,
+                                  const float* dist_far, const float* s_var, const float* anneal_ratio,
                                   const float* d_alphas, int64_t n_rays, int n_samples, float* d_sdf, float* d_grad,
                                   float* d_s_var, void* stream) {
     NA_RAYS_PROLOGUE("neus_alphas_bwd", n_samples)
-    NA_REQUIRE(sdf && grad && dists && ray_unit && s_var && d_alphas && d_sdf && d_grad && d_s_var,
+    NA_REQUIRE(sdf && grad && dists && ray_unit && s_var && anneal_ratio && d_alphas && d_sdf && d_grad && d_s_var,
                "neus_alphas_bwd: null pointer");
     neus_alphas_kernel<true><<<ray_blocks(n_rays), kWarpsPerCta * 32, 0, s>>>(
         sdf, grad, dists, ray_unit, dist_far, s_var, anneal_ratio, d_alphas, n_rays, n_samples, nullptr, d_sdf,
@@ -646,12 +649,12 @@ int launch_render(const RenderArgs& A, float* rgb, float* weights, float* opacit
 }
 
 int fill_render_args(RenderArgs& A, const float* sdf, const float* grad, const float* dists_obj,
-                     const float* ray_unit, const float* dist_far, const float* s_var, float anneal_ratio,
+                     const float* ray_unit, const float* dist_far, const float* s_var, const float* anneal_ratio,
                      const float* rgb_obj, int n_obj, const float* dens_bg, const float* dists_bg,
                      const float* rgb_bg, int n_bg, int64_t n_rays) {
     NA_REQUIRE(n_obj >= 1 && n_bg >= 0 && n_obj + n_bg <= 512, "neus_render: n_obj=%d n_bg=%d unsupported (total <= 512)",
                n_obj, n_bg);
-    NA_REQUIRE(sdf && grad && dists_obj && ray_unit && s_var && rgb_obj, "neus_render: null object pointer");
+    NA_REQUIRE(sdf && grad && dists_obj && ray_unit && s_var && anneal_ratio && rgb_obj, "neus_render: null object pointer");
     NA_REQUIRE(n_bg == 0 || (dens_bg && dists_bg && rgb_bg), "neus_render: null background pointer");
     A = RenderArgs{sdf, grad, dists_obj, ray_unit, dist_far, s_var, rgb_obj, dens_bg, dists_bg, rgb_bg,
                    anneal_ratio, n_obj, n_bg, n_rays};
@@ -660,7 +663,7 @@ int fill_render_args(RenderArgs& A, const float* sdf, const float* grad, const f
 }  // namespace
 
 extern "C" int na_neus_render_fwd(const float* sdf, const float* grad, const float* dists_obj, const float* ray_unit,
-                                  const float* dist_far, const float* s_var, float anneal_ratio,
+                                  const float* dist_far, const float* s_var, const float* anneal_ratio,
                                   const float* rgb_obj, int n_obj, const float* dens_bg, const float* dists_bg,
                                   const float* rgb_bg, int n_bg, int64_t n_rays, float* rgb, float* weights,
                                   float* opacity, void* stream) {
@@ -675,7 +678,7 @@ extern "C" int na_neus_render_fwd(const float* sdf, const float* grad, const flo
 }
 
 extern "C" int na_neus_render_bwd(const float* sdf, const float* grad, const float* dists_obj, const float* ray_unit,
-                                  const float* dist_far, const float* s_var, float anneal_ratio,
+                                  const float* dist_far, const float* s_var, const float* anneal_ratio,
                                   const float* rgb_obj, int n_obj, const float* dens_bg, const float* dists_bg,
                                   const float* rgb_bg, int n_bg, int64_t n_rays, const float* d_rgb,
                                   const float* d_weights, float* d_sdf, float* d_grad, float* d_s_var,

@@ -48,13 +48,25 @@ class PackedSdfMlp:
         if self.k0_pad > 256:
             raise NotImplementedError("input width > 256 unsupported by the fused kernel")
         self.beta = float(beta)
+        self.update_(mlp)
+
+    def update_(self, mlp):
+        """(Re)pack from the module's current weights.  After the first call the packed tensors are updated IN
+        PLACE, so kernels recorded in a CUDA graph keep reading valid, current data from the same addresses."""
+        l0, l1 = mlp.linears
         with torch.no_grad():
-            self.w0_hi, self.w0_lo = pack_weight(l0.effective_weight(), self.k0_pad)
-            self.w1_hi, self.w1_lo = pack_weight(l1.effective_weight(), self.n)
-            self.b0 = l0.bias.detach().float().contiguous()
-            self.b1 = l1.bias.detach().float().contiguous()
-            self.w_head = mlp.linear_sdf.weight.detach().float().reshape(-1).contiguous()
-            self.b_head = mlp.linear_sdf.bias.detach().float().reshape(1).clone()
+            new = dict(zip(("w0_hi", "w0_lo"), pack_weight(l0.effective_weight(), self.k0_pad)))
+            new.update(zip(("w1_hi", "w1_lo"), pack_weight(l1.effective_weight(), self.n)))
+            new["b0"] = l0.bias.detach().float().contiguous()
+            new["b1"] = l1.bias.detach().float().contiguous()
+            new["w_head"] = mlp.linear_sdf.weight.detach().float().reshape(-1).contiguous()
+            new["b_head"] = mlp.linear_sdf.bias.detach().float().reshape(1)
+            for name, t in new.items():
+                cur = getattr(self, name, None)
+                if cur is not None and cur.shape == t.shape and cur.device == t.device:
+                    cur.copy_(t)
+                else:
+                    setattr(self, name, t.clone())
 
     def forward(self, rows, with_sdf=True, with_feat=True, with_hidden=False):
         """rows: [M, K0] fp32 CUDA tensor, unit stride in the last dim (row stride free).

@@ -32,6 +32,9 @@ class Model(torch.nn.Module):
         self.image_size_train = cfg_data.train.image_size
         self.image_size_val = cfg_data.val.image_size
         self.progress = 1.
+        # device copy of min(progress / anneal_end, 1), kept current by set_progress(): kernels read it from
+        # memory, so a captured CUDA graph follows the schedule without re-capture
+        self.register_buffer("_anneal_ratio", torch.ones(1, dtype=torch.float32), persistent=False)
         self.build_model(cfg_model, cfg_data)
         self.sample_dists_from_pdf = partial(nerf_util.sample_dists_from_pdf, intvs_fine=cfg_model.render.num_samples.fine)
 
@@ -49,6 +52,22 @@ class Model(torch.nn.Module):
         self.background_nerf = BackgroundNeRF(cfg_model.background, appear_embed=cfg_model.appear_embed) \
             if cfg_model.background.enabled else None
         self.s_var = torch.nn.Parameter(torch.tensor(cfg_model.object.s_var.init_val, dtype=torch.float32))
+
+    def set_progress(self, progress):
+        """trainer.py:64 sets `model.progress`; this also refreshes the device-side anneal ratio (async copy)."""
+        self.progress = progress
+        ratio = min(progress / self.anneal_end, 1.)
+        self._anneal_synced = ratio
+        # fill_ passes the value as a kernel argument: asynchronous, and no host staging buffer that a CPU running
+        # ahead of the GPU could overwrite before the copy has executed
+        self._anneal_ratio.fill_(ratio)
+
+    def _anneal(self):
+        """The persistent device scalar when it is in sync with self.progress, else None (python value is used)."""
+        expected = min(self.progress / self.anneal_end, 1.)
+        if getattr(self, "_anneal_synced", None) == expected:
+            return self._anneal_ratio
+        return None
 
     def get_param_groups(self, cfg_optim):
         return self.parameters()
@@ -110,7 +129,7 @@ class Model(torch.nn.Module):
         # alphas(object) ++ alphas(background) -> weights -> rgb: one kernel (model.py:132-141)
         rgb, weights, opacity_all = render.neus_render(
             ray_unit, obj["sdfs"], obj["gradients"], obj["dists"], self.s_var, obj["rgbs"], dist_far=far[..., None],
-            progress=self.progress, anneal_end=self.anneal_end,
+            progress=self.progress, anneal_end=self.anneal_end, anneal_ratio=self._anneal(),
             densities_bg=bg["densities"] if bg else None, dists_bg=bg["dists"] if bg else None,
             rgbs_bg=bg["rgbs"] if bg else None)
         if self.white_background:
@@ -119,7 +138,8 @@ class Model(torch.nn.Module):
         opacity = gradient = None
         if not self.training:  # model.py:169-172: object-only weights for opacity / normal
             alphas = render.neus_alphas(ray_unit, obj["sdfs"], obj["gradients"], obj["dists"], self.s_var,
-                                        dist_far=far[..., None], progress=self.progress, anneal_end=self.anneal_end)
+                                        dist_far=far[..., None], progress=self.progress, anneal_end=self.anneal_end,
+                                        anneal_ratio=self._anneal())
             w_obj = render.alpha_compositing_weights(alphas)
             opacity = render.composite(1., w_obj)
             gradient = render.composite(obj["gradients"], w_obj)

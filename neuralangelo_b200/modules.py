@@ -137,13 +137,24 @@ class NeuralSDF(torch.nn.Module):
         key = (getattr(self, "_weights_epoch", 0),) + tuple(p._version for p in self.mlp.parameters()) + \
             (next(self.mlp.parameters()).device,)
         if getattr(self, "_packed_key", None) != key:
-            try:
-                self._packed = PackedSdfMlp(self.mlp, beta=self.cfg_sdf.mlp.activ_params.get("beta", 1.0)) \
-                    if self.cfg_sdf.mlp.activ == "softplus" else None
-            except NotImplementedError:
-                self._packed = None  # architecture outside the fused kernel's envelope: torch ops
+            old = getattr(self, "_packed", None)
+            if old is not None and old.b0.device == key[-1]:
+                old.update_(self.mlp)       # in place: addresses recorded in a CUDA graph stay valid
+            else:
+                try:
+                    self._packed = PackedSdfMlp(self.mlp, beta=self.cfg_sdf.mlp.activ_params.get("beta", 1.0)) \
+                        if self.cfg_sdf.mlp.activ == "softplus" else None
+                except NotImplementedError:
+                    self._packed = None  # architecture outside the fused kernel's envelope: torch ops
             self._packed_key = key
         return self._packed
+
+    def refresh_packed_weights(self):
+        """Re-pack now (eagerly).  The training step calls this right after the optimizer so that the packing
+        never happens inside a captured graph, where it would be frozen."""
+        self.invalidate_packed_weights()
+        if next(self.mlp.parameters()).is_cuda:
+            self._packed_mlp()
 
     def run_mlp(self, rows, with_sdf=True, with_feat=True):
         """rows [...,3+LD] -> [sdf [...,1] | None, feat [...,K] | None]."""

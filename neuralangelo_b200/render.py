@@ -121,6 +121,14 @@ def volume_rendering_alphas_dist(densities, dists, dist_far=None):
     return _DensityAlphas.apply(densities, dists[..., 0].detach(), far)
 
 
+def _anneal_tensor(progress, anneal_end, anneal_ratio, device):
+    """Device scalar for min(progress / anneal_end, 1): either the caller's persistent tensor (kept up to date
+    outside a captured graph) or a fresh one filled from the python value."""
+    if anneal_ratio is not None:
+        return anneal_ratio
+    return torch.full((1,), min(progress / anneal_end, 1.), dtype=torch.float32, device=device)
+
+
 class _NeusAlphas(torch.autograd.Function):
     @staticmethod
     def forward(ctx, sdf, grad, s_var, dists, ray_unit, dist_far, anneal_ratio):
@@ -131,10 +139,10 @@ class _NeusAlphas(torch.autograd.Function):
         rays = sdf.numel() // n
         out = torch.empty_like(sdf)
         _lib.check(_L().na_neus_alphas_fwd(ptr(sdf), ptr(grad), ptr(dists), ptr(ray_unit), ptr(dist_far), ptr(s_var),
-                                           float(anneal_ratio), rays, n, ptr(out), _lib.current_stream()),
+                                           ptr(anneal_ratio), rays, n, ptr(out), _lib.current_stream()),
                    "na_neus_alphas_fwd")
         ctx.save_for_backward(sdf, grad, dists, ray_unit, dist_far, s_var)
-        ctx.anneal_ratio = float(anneal_ratio)
+        ctx.anneal_ratio = anneal_ratio
         return out
 
     @staticmethod
@@ -145,15 +153,15 @@ class _NeusAlphas(torch.autograd.Function):
         d_sdf, d_grad = torch.empty_like(sdf), torch.empty_like(grad)
         d_s = torch.zeros_like(s_var)
         _lib.check(_L().na_neus_alphas_bwd(ptr(sdf), ptr(grad), ptr(dists), ptr(ray_unit), ptr(dist_far), ptr(s_var),
-                                           ctx.anneal_ratio, ptr(f32c(d_alphas)), rays, n, ptr(d_sdf), ptr(d_grad),
+                                           ptr(ctx.anneal_ratio), ptr(f32c(d_alphas)), rays, n, ptr(d_sdf), ptr(d_grad),
                                            ptr(d_s), _lib.current_stream()), "na_neus_alphas_bwd")
         return d_sdf, d_grad, d_s, None, None, None, None
 
 
-def neus_alphas(ray_unit, sdfs, gradients, dists, s_var, dist_far=None, progress=1., anneal_end=0.1):
+def neus_alphas(ray_unit, sdfs, gradients, dists, s_var, dist_far=None, progress=1., anneal_end=0.1, anneal_ratio=None):
     """Model.compute_neus_alphas (model.py:275-292) with _get_iter_cos (:294-298).
     ray_unit [B,R,3], sdfs [B,R,N,1], gradients [B,R,N,3], dists [B,R,N,1], dist_far [B,R,1,1]|None -> [B,R,N]."""
-    anneal_ratio = min(progress / anneal_end, 1.)
+    anneal_ratio = _anneal_tensor(progress, anneal_end, anneal_ratio, sdfs.device)
     far = None if dist_far is None else dist_far.reshape(sdfs.shape[:-2])
     return _NeusAlphas.apply(sdfs[..., 0], gradients, s_var, dists[..., 0].detach(), ray_unit.detach(), far,
                              anneal_ratio)
@@ -174,11 +182,11 @@ class _NeusRender(torch.autograd.Function):
         weights = torch.empty(*lead, n_obj + n_bg, dtype=torch.float32, device=sdf.device) if want_weights else None
         opacity = torch.empty(*lead, dtype=torch.float32, device=sdf.device)
         _lib.check(_L().na_neus_render_fwd(ptr(sdf), ptr(grad), ptr(dists_obj), ptr(ray_unit), ptr(dist_far), ptr(s_var),
-                                           float(anneal_ratio), ptr(rgb_obj), n_obj, ptr(dens_bg), ptr(dists_bg),
+                                           ptr(anneal_ratio), ptr(rgb_obj), n_obj, ptr(dens_bg), ptr(dists_bg),
                                            ptr(rgb_bg), n_bg, rays, ptr(rgb), ptr(weights), ptr(opacity),
                                            _lib.current_stream()), "na_neus_render_fwd")
         ctx.save_for_backward(sdf, grad, s_var, rgb_obj, dens_bg, rgb_bg, dists_obj, ray_unit, dist_far, dists_bg)
-        ctx.anneal_ratio = float(anneal_ratio)
+        ctx.anneal_ratio = anneal_ratio
         ctx.mark_non_differentiable(opacity)
         if weights is None:
             weights = torch.empty(0, device=sdf.device)
@@ -197,7 +205,7 @@ class _NeusRender(torch.autograd.Function):
         d_rgb_bg = torch.empty_like(rgb_bg) if n_bg else None
         dw = f32c(d_weights) if (d_weights is not None and d_weights.numel() == rays * (n_obj + n_bg)) else None
         _lib.check(_L().na_neus_render_bwd(ptr(sdf), ptr(grad), ptr(dists_obj), ptr(ray_unit), ptr(dist_far), ptr(s_var),
-                                           ctx.anneal_ratio, ptr(rgb_obj), n_obj, ptr(dens_bg), ptr(dists_bg),
+                                           ptr(ctx.anneal_ratio), ptr(rgb_obj), n_obj, ptr(dens_bg), ptr(dists_bg),
                                            ptr(rgb_bg), n_bg, rays, ptr(f32c(d_rgb)), ptr(dw), ptr(d_sdf), ptr(d_grad),
                                            ptr(d_s), ptr(d_rgb_obj), ptr(d_dens), ptr(d_rgb_bg), _lib.current_stream()),
                    "na_neus_render_bwd")
@@ -205,10 +213,10 @@ class _NeusRender(torch.autograd.Function):
 
 
 def neus_render(ray_unit, sdfs, gradients, dists, s_var, rgbs, dist_far=None, progress=1., anneal_end=0.1,
-                densities_bg=None, dists_bg=None, rgbs_bg=None, want_weights=True):
+                densities_bg=None, dists_bg=None, rgbs_bg=None, want_weights=True, anneal_ratio=None):
     """One kernel for model.py:132-141: returns (rgb [B,R,3], weights [B,R,No+Nb,1] | None, opacity_all [B,R,1]).
     Object inputs as `neus_alphas` plus rgbs [B,R,No,3]; background: densities [B,R,Nb], dists [B,R,Nb,1], rgbs."""
-    anneal_ratio = min(progress / anneal_end, 1.)
+    anneal_ratio = _anneal_tensor(progress, anneal_end, anneal_ratio, sdfs.device)
     far = None if dist_far is None else dist_far.reshape(sdfs.shape[:-2])
     bg = densities_bg is not None
     rgb, weights, opacity = _NeusRender.apply(

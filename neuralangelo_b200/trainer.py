@@ -42,7 +42,6 @@ class TrainStep:
         self._graph = self._graph_key = self._static = self._static_loss = None
         dev = next(model.parameters()).device
         self._w_dev = torch.zeros(3, dtype=torch.float32, device=dev)
-        self._w_host = torch.zeros(3, dtype=torch.float32).pin_memory() if dev.type == "cuda" else torch.zeros(3)
 
     def lr_factor(self, it):
         """two_steps_with_warmup, misc.py:38-52."""
@@ -57,7 +56,7 @@ class TrainStep:
     def start_of_iteration(self, it):
         """trainer.py:63-74."""
         m = self.model
-        m.progress = it / self.max_iter
+        m.set_progress(it / self.max_iter)
         sdf = m.neural_sdf
         if self.c2f:
             sdf.set_active_levels(it)
@@ -91,10 +90,13 @@ class TrainStep:
         return total
 
     def _upload_weights(self):
-        self._w_host[0] = self.weights["render"]
-        self._w_host[1] = self.weights.get("eikonal", 0.0)
-        self._w_host[2] = self.weights.get("curvature", 0.0)
-        self._w_dev.copy_(self._w_host, non_blocking=True)
+        # by-value fills (kernel arguments), not an async copy from a re-used pinned buffer: the CPU may run several
+        # iterations ahead of the GPU in CUDA-graph mode
+        vals = (self.weights["render"], self.weights.get("eikonal", 0.0), self.weights.get("curvature", 0.0))
+        if vals != getattr(self, "_w_last", None):
+            for i, v in enumerate(vals):
+                self._w_dev[i].fill_(float(v))
+            self._w_last = vals
 
     def _forward_backward(self, data):
         out = self.model(data)
@@ -106,8 +108,7 @@ class TrainStep:
         """Everything that is baked into kernel arguments at capture time."""
         m = self.model
         sdf = m.neural_sdf
-        ratio = min(m.progress / m.anneal_end, 1.0)
-        return (getattr(sdf, "active_levels", None), getattr(sdf, "normal_eps", None), ratio, m.training,
+        return (getattr(sdf, "active_levels", None), getattr(sdf, "normal_eps", None), m.training,
                 tuple((k, tuple(v.shape), v.dtype) for k, v in sorted(data.items())))
 
     def _graphed_forward_backward(self, data):
@@ -142,5 +143,6 @@ class TrainStep:
             loss = self._forward_backward(data)
         grad_scale = parallel.allreduce_gradients(*self.optim.grad_views())
         self.optim.step(grad_scale=grad_scale, lr=self.base_lr * self.lr_factor(it))
+        self.model.neural_sdf.refresh_packed_weights()   # outside any captured graph (see NeuralSDF)
         self.current_iteration += 1
         return loss
