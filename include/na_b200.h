@@ -102,6 +102,21 @@ int na_hashgrid_taps_bwd(const na_hashgrid_desc* desc, const float* x, int64_t n
                          const float* dout, int64_t dout_stride, int64_t dout_tap_stride,
                          float* dtable, void* stream);
 
+/* Same kernels with a free feature layout: element (tap t, point n, level l, feature f) lives at
+ *   t*tap_stride + n*point_stride + l*level_stride + f.
+ * The row layout of na_hashgrid_taps_fwd is (point_stride = row stride, level_stride = F); the LEVEL-MAJOR
+ * PLANE layout [taps][levels][points][F] is (point_stride = F, level_stride = n_points*F, tap_stride =
+ * n_levels*n_points*F): every warp then writes (reads) 512 contiguous bytes instead of sixteen lone 32-byte
+ * sectors, and a level's plane is exactly the K-chunk-major operand image the tcgen05 MLP stages. */
+int na_hashgrid_taps_fwd_strided(const na_hashgrid_desc* desc, const float* table, const float* x,
+                                 int64_t n_points, na_unit_map map, uint32_t active_levels,
+                                 const float* tap_offsets, uint32_t n_taps, float* out, int64_t point_stride,
+                                 int64_t tap_stride, int64_t level_stride, void* stream);
+int na_hashgrid_taps_bwd_strided(const na_hashgrid_desc* desc, const float* x, int64_t n_points,
+                                 na_unit_map map, uint32_t active_levels, const float* tap_offsets,
+                                 uint32_t n_taps, const float* dout, int64_t point_stride, int64_t tap_stride,
+                                 int64_t level_stride, float* dtable, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * NeuS volume rendering and hierarchical resampling (one warp per ray).
  * All tensors fp32 contiguous, [n_rays, n_samples(, k)].  `dist_far` is [n_rays] or NULL (= 1e10,

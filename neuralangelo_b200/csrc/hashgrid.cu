@@ -231,7 +231,7 @@ __global__ void __launch_bounds__(kThreads, 3)
 hashgrid_taps_fwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ table,
                          const float* __restrict__ x, int64_t n_points, na_unit_map map, uint32_t active_levels,
                          const __grid_constant__ TapParams taps, float* __restrict__ out, int64_t out_stride,
-                         int64_t out_tap_stride, const Mapping m) {
+                         int64_t out_tap_stride, int64_t out_level_stride, const Mapping m) {
     using S = Shape<F>;
     using VT = Vec<S::V>;
     __shared__ LevelS sl[NA_MAX_LEVELS];
@@ -252,7 +252,7 @@ hashgrid_taps_fwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
     for (int i = warp * m.points_per_warp + pt_in_warp; i < m.points_per_cta; i += step) {
         const int64_t n = cta_base + i;
         if (n >= n_points) break;
-        float* o = out + n * out_stride + level * F + sub * S::V;
+        float* o = out + n * out_stride + level * out_level_stride + sub * S::V;
         if (!active) {  // coarse-to-fine mask: inactive levels are exactly zero
             for (uint32_t t = 0; t < taps.n; ++t)
                 VT::template store_stream<ALIGNED>(o + t * out_tap_stride, make_float4(0.f, 0.f, 0.f, 0.f), stream);
@@ -315,7 +315,8 @@ __global__ void __launch_bounds__(kThreads, 3)
 hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ x,
                          int64_t n_points, na_unit_map map, uint32_t active_levels,
                          const __grid_constant__ TapParams taps, const float* __restrict__ dout,
-                         int64_t dout_stride, int64_t dout_tap_stride, float* __restrict__ dtable, const Mapping m) {
+                         int64_t dout_stride, int64_t dout_tap_stride, int64_t dout_level_stride,
+                         float* __restrict__ dtable, const Mapping m) {
     using S = Shape<F>;
     using VT = Vec<S::V>;
     __shared__ LevelS sl[NA_MAX_LEVELS];
@@ -335,7 +336,7 @@ hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
     for (int i = warp * m.points_per_warp + pt_in_warp; i < m.points_per_cta; i += step) {
         const int64_t n = cta_base + i;
         if (n >= n_points) break;
-        const float* g = dout + n * dout_stride + level * F + sub * S::V;
+        const float* g = dout + n * dout_stride + level * dout_level_stride + sub * S::V;
         const float x0 = __ldg(x + n * 3 + 0), x1 = __ldg(x + n * 3 + 1), x2 = __ldg(x + n * 3 + 2);
         const Cell c0 = locate_tap(L, map, taps, 0, x0, x1, x2);
         float4 acc[8];
@@ -384,11 +385,13 @@ hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
 // one 128 MiB hashed level is the working set).  Measured on B200, 2^22 random points, default
 // table (profiles/r01_hashgrid_mapping_sweep.md): 1 level/pass is best for a single evaluation,
 // 2 levels/pass for the 7-evaluation tap kernel whose traffic is dominated by feature rows.
-Mapping make_mapping(const na_hashgrid_desc* desc, uint32_t levels, uint32_t n_taps) {
+Mapping make_mapping(const na_hashgrid_desc* desc, uint32_t levels, uint32_t n_taps, bool planes) {
     Mapping m;
     m.lanes_per_level = desc->n_features >= 4 ? desc->n_features / 4 : 1;
     const int max_levels_per_warp = 32 / m.lanes_per_level;
-    int cap = n_taps > 1 ? 2 : 1;
+    // level-major feature planes: consecutive points are consecutive in memory, so one level per pass is both
+    // the coalesced and the L2-friendly choice
+    int cap = (n_taps > 1 && !planes) ? 2 : 1;
     if (const char* e = getenv("NA_HG_GROUP")) cap = atoi(e);  // developer knob for the sweep above
     if (cap > max_levels_per_warp) cap = max_levels_per_warp;
     int lp = 1;  // levels per pass: power of two so that points-per-warp divides the warp
@@ -415,9 +418,10 @@ int validate(const na_hashgrid_desc* desc, const void* a, const void* b, int64_t
     return NA_OK;
 }
 
-bool vec_aligned(const void* p, int64_t stride, int64_t tap_stride, int n_features) {
+bool vec_aligned(const void* p, int64_t stride, int64_t tap_stride, int64_t level_stride, int n_features) {
     const int v = n_features >= 4 ? 4 : 2;
-    return ((uintptr_t)p % (v * sizeof(float)) == 0) && (stride % v == 0) && (tap_stride % v == 0);
+    return ((uintptr_t)p % (v * sizeof(float)) == 0) && (stride % v == 0) && (tap_stride % v == 0) &&
+           (level_stride % v == 0);
 }
 
 int fill_taps(TapParams& tp, const float* tap_offsets, uint32_t n_taps) {
@@ -433,17 +437,17 @@ int fill_taps(TapParams& tp, const float* tap_offsets, uint32_t n_taps) {
 template <int F>
 int launch_fwd(const na_hashgrid_desc* desc, const float* table, const float* x, int64_t n_points, na_unit_map map,
                uint32_t active_levels, const TapParams& tp, float* out, int64_t out_stride, int64_t out_tap_stride,
-               cudaStream_t stream) {
-    const Mapping m = make_mapping(desc, desc->n_levels, tp.n);
+               int64_t out_level_stride, cudaStream_t stream) {
+    const Mapping m = make_mapping(desc, desc->n_levels, tp.n, out_level_stride != F);
     const int64_t blocks = (n_points + m.points_per_cta - 1) / m.points_per_cta;
     NA_REQUIRE(blocks <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
     dim3 grid((unsigned)blocks, m.passes);
-    if (vec_aligned(out, out_stride, out_tap_stride, F))
-        hashgrid_taps_fwd_kernel<F, true><<<grid, kThreads, 0, stream>>>(*desc, table, x, n_points, map, active_levels,
-                                                                         tp, out, out_stride, out_tap_stride, m);
+    if (vec_aligned(out, out_stride, out_tap_stride, out_level_stride, F))
+        hashgrid_taps_fwd_kernel<F, true><<<grid, kThreads, 0, stream>>>(
+            *desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride, out_level_stride, m);
     else
         hashgrid_taps_fwd_kernel<F, false><<<grid, kThreads, 0, stream>>>(
-            *desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride, m);
+            *desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride, out_level_stride, m);
     NA_CHECK_LAUNCH("hashgrid_taps_fwd_kernel");
     return NA_OK;
 }
@@ -451,22 +455,28 @@ int launch_fwd(const na_hashgrid_desc* desc, const float* table, const float* x,
 template <int F>
 int launch_bwd(const na_hashgrid_desc* desc, const float* x, int64_t n_points, na_unit_map map,
                uint32_t active_levels, const TapParams& tp, const float* dout, int64_t dout_stride,
-               int64_t dout_tap_stride, float* dtable, cudaStream_t stream) {
-    const Mapping m = make_mapping(desc, active_levels, tp.n);
+               int64_t dout_tap_stride, int64_t dout_level_stride, float* dtable, cudaStream_t stream) {
+    const Mapping m = make_mapping(desc, active_levels, tp.n, dout_level_stride != F);
     const int64_t blocks = (n_points + m.points_per_cta - 1) / m.points_per_cta;
     NA_REQUIRE(blocks <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
     dim3 grid((unsigned)blocks, m.passes);
-    if (vec_aligned(dout, dout_stride, dout_tap_stride, F))
-        hashgrid_taps_bwd_kernel<F, true><<<grid, kThreads, 0, stream>>>(*desc, x, n_points, map, active_levels, tp,
-                                                                         dout, dout_stride, dout_tap_stride, dtable, m);
+    if (vec_aligned(dout, dout_stride, dout_tap_stride, dout_level_stride, F))
+        hashgrid_taps_bwd_kernel<F, true><<<grid, kThreads, 0, stream>>>(
+            *desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dout_level_stride, dtable, m);
     else
-        hashgrid_taps_bwd_kernel<F, false><<<grid, kThreads, 0, stream>>>(*desc, x, n_points, map, active_levels, tp,
-                                                                          dout, dout_stride, dout_tap_stride, dtable, m);
+        hashgrid_taps_bwd_kernel<F, false><<<grid, kThreads, 0, stream>>>(
+            *desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dout_level_stride, dtable, m);
     NA_CHECK_LAUNCH("hashgrid_taps_bwd_kernel");
     return NA_OK;
 }
 
 }  // namespace
+
+extern "C" int na_hashgrid_taps_fwd_strided(const na_hashgrid_desc*, const float*, const float*, int64_t, na_unit_map,
+                                            uint32_t, const float*, uint32_t, float*, int64_t, int64_t, int64_t, void*);
+extern "C" int na_hashgrid_taps_bwd_strided(const na_hashgrid_desc*, const float*, int64_t, na_unit_map, uint32_t,
+                                            const float*, uint32_t, const float*, int64_t, int64_t, int64_t, float*,
+                                            void*);
 
 extern "C" int na_hashgrid_make_desc(uint32_t n_levels, uint32_t n_features, uint32_t log2_hashmap_size,
                                      uint32_t base_resolution, double per_level_scale, na_hashgrid_desc* desc) {
@@ -514,19 +524,28 @@ extern "C" int na_hashgrid_taps_fwd(const na_hashgrid_desc* desc, const float* t
                                     int64_t n_points, na_unit_map map, uint32_t active_levels,
                                     const float* tap_offsets, uint32_t n_taps, float* out, int64_t out_stride,
                                     int64_t out_tap_stride, void* stream) {
+    return na_hashgrid_taps_fwd_strided(desc, table, x, n_points, map, active_levels, tap_offsets, n_taps, out,
+                                        out_stride, out_tap_stride, desc ? (int64_t)desc->n_features : 0, stream);
+}
+
+extern "C" int na_hashgrid_taps_fwd_strided(const na_hashgrid_desc* desc, const float* table, const float* x,
+                                            int64_t n_points, na_unit_map map, uint32_t active_levels,
+                                            const float* tap_offsets, uint32_t n_taps, float* out,
+                                            int64_t out_stride, int64_t out_tap_stride, int64_t out_level_stride,
+                                            void* stream) {
     na::clear_error();
     if (int rc = validate(desc, table, x, n_points, active_levels)) return rc;
     NA_REQUIRE(n_points == 0 || out != nullptr, "hashgrid fwd: out is null");
-    NA_REQUIRE(out_stride >= (int64_t)desc->n_levels * desc->n_features, "hashgrid fwd: out_stride %lld < L*F",
-               (long long)out_stride);
+    NA_REQUIRE(out_level_stride >= (int64_t)desc->n_features && out_stride >= (int64_t)desc->n_features,
+               "hashgrid fwd: point / level strides must be >= F");
     TapParams tp;
     if (int rc = fill_taps(tp, tap_offsets, n_taps)) return rc;
     if (n_points == 0) return NA_OK;
     cudaStream_t s = (cudaStream_t)stream;
     switch (desc->n_features) {
-        case 8: return launch_fwd<8>(desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride, s);
-        case 4: return launch_fwd<4>(desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride, s);
-        default: return launch_fwd<2>(desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride, s);
+        case 8: return launch_fwd<8>(desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride, out_level_stride, s);
+        case 4: return launch_fwd<4>(desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride, out_level_stride, s);
+        default: return launch_fwd<2>(desc, table, x, n_points, map, active_levels, tp, out, out_stride, out_tap_stride, out_level_stride, s);
     }
 }
 
@@ -534,20 +553,29 @@ extern "C" int na_hashgrid_taps_bwd(const na_hashgrid_desc* desc, const float* x
                                     uint32_t active_levels, const float* tap_offsets, uint32_t n_taps,
                                     const float* dout, int64_t dout_stride, int64_t dout_tap_stride, float* dtable,
                                     void* stream) {
+    return na_hashgrid_taps_bwd_strided(desc, x, n_points, map, active_levels, tap_offsets, n_taps, dout, dout_stride,
+                                        dout_tap_stride, desc ? (int64_t)desc->n_features : 0, dtable, stream);
+}
+
+extern "C" int na_hashgrid_taps_bwd_strided(const na_hashgrid_desc* desc, const float* x, int64_t n_points,
+                                            na_unit_map map, uint32_t active_levels, const float* tap_offsets,
+                                            uint32_t n_taps, const float* dout, int64_t dout_stride,
+                                            int64_t dout_tap_stride, int64_t dout_level_stride, float* dtable,
+                                            void* stream) {
     na::clear_error();
     if (int rc = validate(desc, dtable, x, n_points, active_levels)) return rc;
     NA_REQUIRE(n_points == 0 || dout != nullptr, "hashgrid bwd: dout is null");
-    NA_REQUIRE(dout_stride >= (int64_t)desc->n_levels * desc->n_features, "hashgrid bwd: dout_stride %lld < L*F",
-               (long long)dout_stride);
+    NA_REQUIRE(dout_level_stride >= (int64_t)desc->n_features && dout_stride >= (int64_t)desc->n_features,
+               "hashgrid bwd: point / level strides must be >= F");
     NA_REQUIRE((uintptr_t)dtable % 16 == 0, "hashgrid bwd: dtable must be 16-byte aligned");
     TapParams tp;
     if (int rc = fill_taps(tp, tap_offsets, n_taps)) return rc;
     if (n_points == 0 || active_levels == 0) return NA_OK;
     cudaStream_t s = (cudaStream_t)stream;
     switch (desc->n_features) {
-        case 8: return launch_bwd<8>(desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dtable, s);
-        case 4: return launch_bwd<4>(desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dtable, s);
-        default: return launch_bwd<2>(desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dtable, s);
+        case 8: return launch_bwd<8>(desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dout_level_stride, dtable, s);
+        case 4: return launch_bwd<4>(desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dout_level_stride, dtable, s);
+        default: return launch_bwd<2>(desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dout_level_stride, dtable, s);
     }
 }
 

@@ -78,6 +78,36 @@ def scatter_taps(desc, x, unit_map, active_levels, tap_offsets, dout, dtable):
     return dtable
 
 
+def encode_taps_planes(desc, table, x, unit_map, active_levels, tap_offsets, out=None):
+    """Level-major feature planes: out[t, l, n, f] = feature f of level l at x[n] + tap_offsets[t]."""
+    _lib.require_cuda(table, x)
+    x = _as_points(x)
+    n, L, F = x.shape[0], desc.n_levels, desc.n_features
+    taps, n_taps = _taps_array(tap_offsets)
+    if out is None:
+        out = torch.empty((n_taps, L, n, F), dtype=_F32, device=x.device)
+    assert out.is_contiguous() and out.shape == (n_taps, L, n, F)
+    rc = _lib.lib().na_hashgrid_taps_fwd_strided(ctypes.byref(desc), _lib.ptr(table), _lib.ptr(x), n, unit_map,
+                                                 int(active_levels), taps, n_taps, _lib.ptr(out), F, L * n * F, n * F,
+                                                 _lib.current_stream())
+    _lib.check(rc, "na_hashgrid_taps_fwd_strided")
+    return out
+
+
+def scatter_taps_planes(desc, x, unit_map, active_levels, tap_offsets, dout, dtable):
+    """dtable += backward of encode_taps_planes for dout[t, l, n, f] (contiguous)."""
+    _lib.require_cuda(dtable, x, dout)
+    x = _as_points(x)
+    n, L, F = x.shape[0], desc.n_levels, desc.n_features
+    taps, n_taps = _taps_array(tap_offsets)
+    assert dout.is_contiguous() and dout.shape == (n_taps, L, n, F) and dout.dtype == _F32
+    rc = _lib.lib().na_hashgrid_taps_bwd_strided(ctypes.byref(desc), _lib.ptr(x), n, unit_map, int(active_levels), taps,
+                                                 n_taps, _lib.ptr(dout), F, L * n * F, n * F, _lib.ptr(dtable),
+                                                 _lib.current_stream())
+    _lib.check(rc, "na_hashgrid_taps_bwd_strided")
+    return dtable
+
+
 class _HashGridTaps(torch.autograd.Function):
     """Autograd wrapper: gradient w.r.t. the table only (numerical-gradient mode never asks for d/dx,
     modules.py:132-175; analytical mode, modules.py:117-130, is outside this path)."""

@@ -45,6 +45,18 @@ for name, taps in (("fwd1", six[:1]), ("fwd7", six)):
     by = len(taps) * n * (12 + 512) + 2 * table.numel() * 4
     res[name.replace("fwd", "bwd")] = dict(ms=med, min_ms=mn, algo_GB=by / 1e9, GBps=by / med / 1e6)
     del out, dout, dt
+# level-major plane layout
+for name, taps in (("fwd1_planes", six[:1]), ("fwd7_planes", six)):
+    out = torch.empty(len(taps), 16, n, 8, device=dev)
+    med, mn = timeit(lambda: hashgrid.encode_taps_planes(desc, table, x, um, 16, taps, out=out))
+    by = len(taps) * n * (12 + 512) + table.numel() * 4
+    res[name] = dict(ms=med, min_ms=mn, algo_GB=by / 1e9, GBps=by / med / 1e6)
+    dout = torch.randn_like(out)
+    dt = torch.zeros_like(table)
+    med, mn = timeit(lambda: hashgrid.scatter_taps_planes(desc, x, um, 16, taps, dout, dt))
+    by = len(taps) * n * (12 + 512) + 2 * table.numel() * 4
+    res[name.replace("fwd", "bwd")] = dict(ms=med, min_ms=mn, algo_GB=by / 1e9, GBps=by / med / 1e6)
+    del out, dout, dt
 # sorted points (spatially coherent) for comparison
 xs = x[torch.argsort((x * 64).floor().mul(torch.tensor([4096., 64., 1.], device=dev)).sum(-1))].contiguous()
 out = torch.empty(1, n, 128, device=dev)

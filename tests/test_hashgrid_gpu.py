@@ -171,3 +171,22 @@ def test_errors_are_reported(na_lib, cuda_device):
     assert rc == -1 and b"active_levels" in _lib.lib().na_last_error()
     with pytest.raises(_lib.NaError):
         hashgrid.encode_taps(desc, torch.zeros(10), torch.rand(4, 3), _lib.UnitMap(0.0, 1.0), 4, ((0, 0, 0),))
+
+
+def test_plane_layout_matches_row_layout(default_grid, cuda_device):
+    """[taps][levels][points][F] planes hold the same numbers as the [taps][points][L*F] rows, forward and backward."""
+    from neuralangelo_b200 import hashgrid, _lib
+    tbl, table, desc, table_d = default_grid
+    pts = ((_unit_ball_points(4099, 8) - 0.5) * 4.0).to(cuda_device)
+    um = _lib.UnitMap(-2.0, 0.25)
+    taps = SIX_TAPS(float(np.float32(1.0 / 2049)))
+    rows = hashgrid.encode_taps(desc, table_d, pts, um, 13, taps)                       # [7, N, 128]
+    planes = hashgrid.encode_taps_planes(desc, table_d, pts, um, 13, taps)              # [7, 16, N, 8]
+    assert torch.equal(planes.permute(0, 2, 1, 3).reshape(7, -1, 128), rows)
+    g = torch.Generator(device=cuda_device).manual_seed(2)
+    dout = torch.randn(7, 4099, 128, device=cuda_device, generator=g)
+    d_rows = torch.zeros_like(table_d)
+    hashgrid.scatter_taps(desc, pts, um, 13, taps, dout, d_rows)
+    d_planes = torch.zeros_like(table_d)
+    hashgrid.scatter_taps_planes(desc, pts, um, 13, taps, dout.view(7, -1, 16, 8).permute(0, 2, 1, 3).contiguous(), d_planes)
+    assert (d_rows - d_planes).abs().max().item() <= 1e-5 * d_rows.abs().max().item()
