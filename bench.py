@@ -160,7 +160,8 @@ def run_reference(args, rank, world):
 def workload_config():
     return {"workload": "BASELINE.json configs[1]: hash-grid encode fwd+bwd, 16 levels x 8 features, 2^22-entry "
                         "hashmap, 2^22 points/GPU, centre + 6 taps (eps 1/2048)", "points_per_gpu": N_POINTS,
-            "taps": 7, "table_bytes": 45724048 * 8 * 4, "l2_policy": "inputs_exceed_l2 (30 GB of rows + 1.46 GB "
+            "taps": 7, "table_bytes": 45724048 * 8 * 4, "feature_layout": "level-major planes [taps][levels][points][8] fp32",
+            "l2_policy": "inputs_exceed_l2 (30 GB of rows + 1.46 GB "
             "table per step vs 126 MB L2)", "parallelism": "points sharded across ranks, no data-path collective"}
 
 
@@ -182,8 +183,9 @@ def run_ours(args, rank, local_rank, world):
     pts = unit_ball_points(N_POINTS, rank, dev)
     pts_host = pts.cpu().pin_memory()
     g1 = torch.Generator(device=dev).manual_seed(1 + rank)
-    dout = torch.randn(len(taps), N_POINTS, 128, device=dev, generator=g1)
-    out = torch.empty(len(taps), N_POINTS, 128, device=dev)
+    # native feature layout: level-major planes [taps][levels][points][F]
+    dout = torch.randn(len(taps), 16, N_POINTS, 8, device=dev, generator=g1)
+    out = torch.empty(len(taps), 16, N_POINTS, 8, device=dev)
     dtable = torch.zeros_like(table)
     pts_dev = torch.empty_like(pts)
     result_host = torch.empty(129, dtype=torch.float32).pin_memory()
@@ -194,10 +196,10 @@ def run_ours(args, rank, local_rank, world):
         dtable.zero_()
         if ev:
             ev[0].record()
-        hashgrid.encode_taps(desc, table, x, um, 16, taps, out=out)
+        hashgrid.encode_taps_planes(desc, table, x, um, 16, taps, out=out)
         if ev:
             ev[1].record()
-        hashgrid.scatter_taps(desc, x, um, 16, taps, dout, dtable)
+        hashgrid.scatter_taps_planes(desc, x, um, 16, taps, dout, dtable)
         if ev:
             ev[2].record()
         launches[0] += 2
@@ -205,7 +207,7 @@ def run_ours(args, rank, local_rank, world):
     def step_e2e():
         pts_dev.copy_(pts_host, non_blocking=True)
         step(pts_dev)
-        res = torch.cat([out[0, 0], dtable[:262144].sum().reshape(1)])
+        res = torch.cat([out[0, :, 0, :].reshape(-1), dtable[:262144].sum().reshape(1)])
         result_host.copy_(res, non_blocking=True)
         torch.cuda.current_stream().synchronize()
 

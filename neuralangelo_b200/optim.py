@@ -75,10 +75,16 @@ class FusedAdamW:
         n_active, _ = self.active_prefix()
         return self.flat_g, self.table.grad[:n_active]
 
-    def step(self, grad_scale=1.0, lr=None):
+    def step(self, grad_scale=1.0, lr=None, table_chunks=None, small_ready=None):
+        """One optimizer step.  `table_chunks`: optional list of (lo, hi, wait_fn) covering the active table prefix;
+        each chunk's update is issued after wait_fn() (its gradient all-reduce), so the update of chunk i overlaps
+        the all-reduce of chunk i+1 running on the communication stream.  `small_ready` likewise gates the flat
+        bucket."""
         lr = self.lr if lr is None else lr
         self.step_count += 1
         b1, b2 = self.betas
+        if small_ready is not None:
+            small_ready()
         stream = _lib.current_stream()
         _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
                                       self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
@@ -100,11 +106,82 @@ class FusedAdamW:
                 _lib.check(_L().na_scale_inplace(ptr(self.table[lo:]), hi - lo, math.exp(self.pending_log_decay), stream),
                            "na_scale_inplace")
             self.applied_levels = active
-        _lib.check(_L().na_adamw_step(ptr(self.table), ptr(self.table.grad), ptr(self.table_m), ptr(self.table_v),
-                                      n_active, lr, b1, b2, self.eps, self.weight_decay, self.step_count, grad_scale, 1,
-                                      stream), "na_adamw_step")
+        chunks = list(table_chunks) if table_chunks else [(0, n_active, None)]
+        assert chunks[0][0] == 0, "table_chunks must start at 0"
+        if chunks[-1][1] < n_active:      # eager (non-lazy) mode also steps the levels beyond the reduced prefix
+            chunks.append((chunks[-1][1], n_active, None))
+        for lo, hi, wait_fn in chunks:
+            if wait_fn is not None:
+                wait_fn()
+            _lib.check(_L().na_adamw_step(ptr(self.table[lo:]), ptr(self.table.grad[lo:]), ptr(self.table_m[lo:]),
+                                          ptr(self.table_v[lo:]), hi - lo, lr, b1, b2, self.eps, self.weight_decay,
+                                          self.step_count, grad_scale, 1, stream), "na_adamw_step")
         if self.lazy and self.applied_levels < self.n_levels:
             self.pending_log_decay += math.log1p(-lr * self.weight_decay)
+
+    def step_sharded(self, rank, world, lr=None, comm=None):
+        """Data-parallel step with the table update SHARDED across ranks (ZeRO-1 style):
+            reduce-scatter(active gradient prefix) -> AdamW on this rank's 1/world slice -> all-gather(parameters).
+        Same bytes on the wire as the all-reduce DDP issues (get_trainer.py:81-88), same arithmetic per element
+        (every element is still updated exactly once, by its owner), but the HBM-bound optimizer pass over the
+        1.46 GB table shrinks by `world`.  Slices are equal parts of the ACTIVE prefix; when the prefix grows (a
+        new level every 5000 iterations) the moment buffers are first all-gathered so that every rank holds the
+        full state, then ownership is re-cut.  The small flat bucket is all-reduced and stepped everywhere."""
+        import torch.distributed as dist
+        comm = comm or dist
+        lr = self.lr if lr is None else lr
+        self.step_count += 1
+        b1, b2 = self.betas
+        stream = _lib.current_stream()
+        scale = 1.0 / world
+        small = comm.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, async_op=True)
+        n_active, active = self.active_prefix()
+        g, p = self.table.grad, self.table
+        assert n_active % (4 * world) == 0, "active prefix must split evenly across ranks"
+        old = getattr(self, "_shard_prefix", None)
+        if old is not None and old != n_active:     # ownership is about to move: make the moments whole first
+            part = old // world
+            for buf in (self.table_m, self.table_v):
+                comm.all_gather_into_tensor(buf[:old], buf[rank * part:(rank + 1) * part].clone())
+        self._shard_prefix = n_active
+        if active > self.applied_levels:      # levels activated this step catch up on their skipped weight decay
+            lo = self.level_end[self.applied_levels - 1] if self.applied_levels > 0 else 0
+            hi = self.level_end[active - 1]
+            if self.pending_log_decay != 0.0:
+                _lib.check(_L().na_scale_inplace(ptr(p[lo:]), hi - lo, math.exp(self.pending_log_decay), stream),
+                           "na_scale_inplace")
+            self.applied_levels = active
+        part = n_active // world
+        a, b = rank * part, (rank + 1) * part
+        rs = comm.reduce_scatter_tensor(g[a:b], g[:n_active], op=dist.ReduceOp.SUM, async_op=True)
+        small.wait()
+        _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
+                                      self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
+                                      scale, 1, stream), "na_adamw_step")
+        rs.wait()
+        _lib.check(_L().na_adamw_step(ptr(p[a:]), ptr(g[a:]), ptr(self.table_m[a:]), ptr(self.table_v[a:]), b - a, lr, b1,
+                                      b2, self.eps, self.weight_decay, self.step_count, scale, 1, stream), "na_adamw_step")
+        ag = comm.all_gather_into_tensor(p[:n_active], p[a:b], async_op=True)
+        if a > 0:                              # the other ranks' slices still hold this rank's local gradients
+            g[:a].zero_()
+        if b < n_active:
+            g[b:n_active].zero_()
+        ag.wait()
+        sdf_mod = getattr(self.model, "neural_sdf", None)
+        if sdf_mod is not None and hasattr(sdf_mod, "invalidate_packed_weights"):
+            sdf_mod.invalidate_packed_weights()
+        if self.lazy and self.applied_levels < self.n_levels:
+            self.pending_log_decay += math.log1p(-lr * self.weight_decay)
+
+    def gather_optimizer_state(self, rank, world, comm=None):
+        """Make exp_avg / exp_avg_sq whole on every rank (before a checkpoint, or before leaving sharded mode)."""
+        import torch.distributed as dist
+        comm = comm or dist
+        old = getattr(self, "_shard_prefix", None)
+        if old:
+            part = old // world
+            for buf in (self.table_m, self.table_v):
+                comm.all_gather_into_tensor(buf[:old], buf[rank * part:(rank + 1) * part].clone())
 
     def flush_inactive_decay(self):
         """Bring the still-inactive levels up to date (call before saving a checkpoint)."""

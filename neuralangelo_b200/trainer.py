@@ -141,8 +141,14 @@ class TrainStep:
             loss = self._graphed_forward_backward(data)
         else:
             loss = self._forward_backward(data)
-        grad_scale = parallel.allreduce_gradients(*self.optim.grad_views())
-        self.optim.step(grad_scale=grad_scale, lr=self.base_lr * self.lr_factor(it))
+        lr = self.base_lr * self.lr_factor(it)
+        world = parallel.world_size()
+        if world > 1 and self.optim.table is not None and self.optim.lazy:
+            import torch.distributed as dist
+            self.optim.step_sharded(dist.get_rank(), world, lr=lr)     # reduce-scatter / owner update / all-gather
+        else:
+            grad_scale = parallel.allreduce_gradients(*self.optim.grad_views())
+            self.optim.step(grad_scale=grad_scale, lr=lr)
         self.model.neural_sdf.refresh_packed_weights()   # outside any captured graph (see NeuralSDF)
         self.current_iteration += 1
         return loss
