@@ -151,6 +151,22 @@ def concatenate(meshes):
                 np.concatenate([m.visual.vertex_colors for m in meshes]))
 
 
+@torch.no_grad()
+def extract_texture(xyz, neural_rgb, neural_sdf, appear_embed):
+    """mesh.py:52-65: per-vertex colour = RGB network at the vertex with view direction = -normal, normal from
+    the SDF's numerical gradient, appearance embedding zero.  xyz: numpy [N,3] -> uint8 [N,3]."""
+    device = next(neural_sdf.parameters()).device
+    pts = torch.from_numpy(np.asarray(xyz)).float().to(device)[None, None]      # [1,1,N,3]
+    sdfs, feats = neural_sdf(pts)
+    gradients, _ = neural_sdf.compute_gradients(pts, training=False, sdf=sdfs)
+    normals = torch.nn.functional.normalize(gradients, dim=-1)
+    app = None
+    if appear_embed is not None:
+        app = torch.zeros([1, 1, pts.shape[2], appear_embed.embedding_dim], device=device)
+    rgbs = neural_rgb.forward(pts, normals, -normals, feats, app=app)
+    return (rgbs.squeeze(0).squeeze(0).cpu().numpy() * 255).astype(np.uint8)
+
+
 class LatticeGrid(torch.utils.data.Dataset):
     """Blocked lattice over `bounds` with step `intv` (mesh.py:68-100): same grids (torch.arange on the CPU,
     float32), same block count / index order / 1-slice overlap, truncated at the far faces."""

@@ -122,3 +122,18 @@ def test_no_grad_sdf_uses_fused_mlp_and_matches_autograd_path(na_lib, cuda_devic
         model.neural_sdf.mlp.linear_sdf.bias.add_(0.25)
         shifted = model.neural_sdf.sdf(pts)
     torch.testing.assert_close(shifted, only + 0.25, rtol=0, atol=1e-6)
+
+
+def test_textured_mesh_extraction_with_the_model(na_lib, cuda_device, golden_dir):
+    """extract_mesh driven by the model's own SDF (sign flipped as scripts/extract_mesh.py:85) with per-vertex
+    colours from extract_texture: finite colours, one per vertex, faces index valid vertices."""
+    from functools import partial
+    from neuralangelo_b200 import mesh
+    G = _load(golden_dir, 6)
+    model = _build(G, 6, cuda_device).eval()
+    sdf_func = lambda x: -model.neural_sdf.sdf(x)
+    tex = partial(mesh.extract_texture, neural_sdf=model.neural_sdf, neural_rgb=model.neural_rgb, appear_embed=None)
+    m = mesh.extract_mesh(sdf_func, np.array([[-1.0, 1.0]] * 3), intv=2.0 / 48, block_res=32, texture_func=tex)
+    assert len(m.vertices) > 100 and m.faces.max() < len(m.vertices)
+    assert m.visual.vertex_colors.shape == (len(m.vertices), 4) and m.visual.vertex_colors.dtype == np.uint8
+    assert np.linalg.norm(m.vertices, axis=1).max() < 1.0          # bounding-sphere filter (mesh.py:136-148)
