@@ -267,6 +267,32 @@ int na_sdf_mlp_bwd(int64_t m, int n, int k0, int k0_pad, int two_layer, const fl
                    const float* w_head, float beta, const float* norms, float* dz1, float* dz0, float* dx,
                    int64_t ld_dx, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Generic fused MLP forward on tcgen05: a program of stages run per 128-row tile with all intermediate
+ * activations on chip.  Stage = [epilogue of the previous product: + bias, activation (0 none, 1 relu,
+ * 2 softplus(act_param), 3 sigmoid) -> next A operand (epi_to_a) and/or global `out` and/or `save`]
+ * [load in_cols (<= 256) columns of a global input into the A operand] [product D (+)= A W^T, n_out <= 256,
+ * k_chunks*8 <= 256 columns of A; weights packed like na_sdf_mlp_fwd's].  Wide inputs, skip connections,
+ * 257-wide layers and chained networks are sequences of such stages (see neuralangelo_b200/fused_chain.py).
+ * Replaces: MLPwithSkipConnection.forward, projects/nerf/utils/nerf_util.py:186-196, as used by
+ *   NeuralRGB.forward (projects/neuralangelo/utils/modules.py:209-220) and BackgroundNeRF.forward (:270-285).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct na_mlp_stage {
+    int32_t has_epi, act, n_valid, epi_to_a;
+    float act_param;
+    int32_t in_col, in_cols, has_gemm, k_chunks, n_out, accumulate, reserved;
+    const float* bias;
+    float* out;
+    int64_t out_ld;
+    float* save;
+    int64_t save_ld;
+    const float* in;
+    int64_t in_ld;
+    const void* w_hi;
+    const void* w_lo;
+} na_mlp_stage;
+int na_mlp_chain_fwd(const na_mlp_stage* stages, int n_stages, int64_t m, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -36,6 +36,17 @@ class UnitMap(ctypes.Structure):
     _fields_ = [("vol_min", ctypes.c_float), ("inv_extent", ctypes.c_float)]
 
 
+class MlpStage(ctypes.Structure):
+    """Mirror of `na_mlp_stage`."""
+    _fields_ = [("has_epi", ctypes.c_int32), ("act", ctypes.c_int32), ("n_valid", ctypes.c_int32),
+                ("epi_to_a", ctypes.c_int32), ("act_param", ctypes.c_float), ("in_col", ctypes.c_int32),
+                ("in_cols", ctypes.c_int32), ("has_gemm", ctypes.c_int32), ("k_chunks", ctypes.c_int32),
+                ("n_out", ctypes.c_int32), ("accumulate", ctypes.c_int32), ("reserved", ctypes.c_int32),
+                ("bias", ctypes.c_void_p), ("out", ctypes.c_void_p), ("out_ld", ctypes.c_int64),
+                ("save", ctypes.c_void_p), ("save_ld", ctypes.c_int64), ("inp", ctypes.c_void_p),
+                ("in_ld", ctypes.c_int64), ("w_hi", ctypes.c_void_p), ("w_lo", ctypes.c_void_p)]
+
+
 class NaError(RuntimeError):
     pass
 
@@ -84,6 +95,7 @@ def _declare(lib):
                                           vp, vp, vp, vp, vp, f32, vp, vp, i64, vp, i64, vp]),
         "na_sdf_mlp_bwd": (ctypes.c_int, [i64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, vp, vp, i64, vp,
                                           vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, i64, vp]),
+        "na_mlp_chain_fwd": (ctypes.c_int, [ctypes.POINTER(MlpStage), ctypes.c_int, i64, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -25,12 +25,12 @@
 //     (k / 8) * (R / 8 * 128) + (row / 8) * 128 + (row % 8) * 16 + (k % 8) * 2   bytes,
 // so a thread that owns one row writes its eight-column chunks with conflict-free 16-byte stores and the
 // host packs the weights once per optimiser step into the exact shared-memory image.
-#include "na_common.cuh"
-#include <cuda_fp16.h>
+#include "tc_common.cuh"
 
 namespace {
 
-constexpr int kTileM = 128;
+using namespace na_tc;
+
 constexpr int kComputeWarps = 8;
 constexpr int kComputeThreads = kComputeWarps * 32;
 constexpr int kThreads = kComputeThreads + 64;  // + MMA warp + loader warp
@@ -38,7 +38,6 @@ constexpr int kStages = 5;
 constexpr int kBlockK = 16;                     // K elements per weight-ring stage (one UMMA k-step)
 constexpr int kMaxK = 256;                      // widest A operand held in shared memory
 constexpr int kMaxN = 256;
-constexpr float kLoScale = 2048.f, kLoInv = 1.f / 2048.f;
 
 constexpr int kABytes = kTileM * kMaxK * 2;             // one fp16 A image (hi or lo): 64 KB
 constexpr int kBStageBytes = 2 * kMaxN * kBlockK * 2;   // W_hi block + W_lo block: 32 KB
@@ -68,99 +67,6 @@ struct MlpParams {
     float* hidden_out;    // [M, N] layer-0 activations (for the backward), stride ld_hidden, or null
     int64_t ld_hidden;
 };
-
-// ---------------------------------------------------------------- PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-// Bounded wait: a protocol bug must trap, not hang the GPU.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done = 0;
-    for (uint32_t spin = 0; !done; ++spin) {
-        asm volatile(
-            "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-            : "=r"(done)
-            : "r"(bar), "r"(parity)
-            : "memory");
-        if (spin > (1u << 24)) __trap();
-    }
-}
-__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"(src), "r"(bytes), "r"(bar)
-                 : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                           uint32_t accumulate) {
-    asm volatile(
-        "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}" ::"r"(d_tmem),
-        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,"
-        "%29,%30,%31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr)
-        : "memory");
-}
-__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// K-major, no swizzle: LBO = byte stride between core matrices adjacent in K, SBO = between 8-row groups.
-__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    uint64_t d = 0;
-    d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
-    d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
-    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
-    d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
-    return d;                // layout type 0 (no swizzle), base offset 0
-}
-
-__device__ __forceinline__ uint32_t make_idesc(int m, int n) {
-    // c_format F32 (bits 4-5 = 1), a/b format F16 (0), both K-major (0), N>>3 at bit 17, M>>4 at bit 24
-    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
-}
-
-__device__ __forceinline__ void split_f16(float v, __half& hi, __half& lo) {
-    v = fminf(fmaxf(v, -65504.f), 65504.f);
-    hi = __float2half_rn(v);
-    lo = __float2half_rn((v - __half2float(hi)) * kLoScale);
-}
-
-__device__ __forceinline__ uint32_t pack2(__half a, __half b) {
-    return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
-}
-
-// softplus_beta(x) = max(x,0) + log(1 + exp(-|beta x|)) / beta.  Differs from torch's thresholded form
-// (x when beta*x > 20) by < exp(-20)/beta; the fast exp/log intrinsics are accurate to ~1e-7 ABSOLUTE on the
-// log term, i.e. ~1e-9 on the result for beta = 100 -- far below the fp32 rounding of the sums around it.
-__device__ __forceinline__ float softplus(float x, float beta, float inv_beta) {
-    return fmaxf(x, 0.f) + __logf(1.f + __expf(-fabsf(beta * x))) * inv_beta;
-}
-
-// Byte offset of the 16-byte chunk holding (row, k..k+7) inside an A image of kTileM rows.
-__device__ __forceinline__ uint32_t a_chunk_offset(int row, int kchunk) {
-    return (uint32_t)kchunk * (kTileM / 8 * 128) + (uint32_t)(row >> 3) * 128 + (uint32_t)(row & 7) * 16;
-}
 
 // ---------------------------------------------------------------- the kernel
 __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_constant__ MlpParams P) {

@@ -110,3 +110,63 @@ def test_fused_sdf_mlp_backward(na_lib, cuda_device, with_feat, m):
         r = ref[k]
         rel = (p.grad.cpu().double() - r).norm().item() / max(r.norm().item(), 1e-30)
         assert rel <= 2e-3, (k, rel)       # TF32 weight-gradient GEMMs
+
+
+def _rgb_mlp(seed=0):
+    from neuralangelo_b200.mlp import MLPwithSkipConnection
+    import torch.nn.functional as F
+    torch.manual_seed(seed)
+    return MLPwithSkipConnection([278, 256, 256, 256, 256, 3], activ=F.relu, use_weightnorm=True)
+
+
+def test_fused_chain_colour_mlp_forward_and_backward(na_lib, cuda_device):
+    """278 -> 256 x4 -> 3 (+ sigmoid): input wider than the 256-column A operand (two accumulating products)."""
+    from neuralangelo_b200 import fused_chain
+    mlp = _rgb_mlp()
+    g = torch.Generator().manual_seed(1)
+    m = 128 * 3 + 5
+    x = torch.randn(m, 278, generator=g) * 0.5
+    tgt = torch.rand(m, 3, generator=g)
+    md = mlp.double()
+    xd = x.double().requires_grad_(True)
+    ref = md(xd).sigmoid()
+    ((ref - tgt.double()) ** 2).sum().backward()
+    ref_g = {k: p.grad.clone() for k, p in md.named_parameters()}
+    mlp = mlp.float().to(cuda_device)
+    for p in mlp.parameters():
+        p.grad = None
+    xk = x.to(cuda_device).requires_grad_(True)
+    with torch.no_grad():
+        out_ng = fused_chain.mlp_forward(mlp, xk.detach(), final_act="sigmoid")
+    assert (out_ng.cpu().double() - ref.detach()).abs().max().item() <= 2e-6
+    out = fused_chain.fused_mlp(mlp, xk, final_act="sigmoid")
+    assert torch.equal(out.detach(), out_ng)
+    ((out - tgt.to(cuda_device)) ** 2).sum().backward()
+    assert (xk.grad.cpu().double() - xd.grad).abs().max().item() <= 1e-5 * xd.grad.abs().max().item() + 1e-9
+    for k, p in mlp.named_parameters():
+        rel = (p.grad.cpu().double() - ref_g[k]).norm().item() / max(ref_g[k].norm().item(), 1e-30)
+        assert rel <= 1e-5, (k, rel)       # fp32 library GEMMs in this test (conftest disables TF32)
+
+
+def test_fused_chain_background_nerf(na_lib, cuda_device):
+    """The whole BackgroundNeRF (8-layer skip MLP, 257-wide last layer split into density + feature, chained
+    view-dependent colour MLP) in one launch vs the module's own torch forward."""
+    from neuralangelo_b200 import fused_chain
+    from neuralangelo_b200.config import default_model_config
+    from neuralangelo_b200.modules import BackgroundNeRF
+    torch.manual_seed(3)
+    cfg = default_model_config()
+    bg = BackgroundNeRF(cfg.background, appear_embed=cfg.appear_embed)
+    g = torch.Generator().manual_seed(2)
+    m = 1000
+    pts = torch.randn(m, 3, generator=g) * 3 + 1.5
+    rays = torch.nn.functional.normalize(torch.randn(m, 3, generator=g), dim=-1)
+    bgd = bg.double()
+    ref_rgb, ref_dens = bgd(pts.double(), rays.double(), None)
+    bg = bg.float().to(cuda_device)
+    with torch.no_grad():
+        enc = bg.encode(pts.to(cuda_device)).contiguous()
+        venc = bg.encode_view(rays.to(cuda_device)).contiguous()
+        rgb, dens = fused_chain.background_forward(bg, enc, venc)
+    assert (rgb.cpu().double() - ref_rgb).abs().max().item() <= 5e-6
+    assert (dens.cpu().double() - ref_dens).abs().max().item() <= 5e-6 * max(ref_dens.abs().max().item(), 1.0)
