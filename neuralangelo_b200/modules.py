@@ -244,6 +244,19 @@ class NeuralSDF(torch.nn.Module):
         return gradient, hessian
 
 
+# The colour / background networks run on the tcgen05 chain kernel whenever no autograd graph is needed
+# (validation renders, texture extraction).  With a graph the default is the reference's own arithmetic -- library
+# GEMMs, TF32 when the trainer allows it (imaginaire/trainers/base.py:172-175): measured on B200 the fused forward
+# with saved activations plus a library backward is ~8 % slower per training step than cuBLAS TF32 end to end
+# (profiles/r01_measurements.md), so it is opt-in until the backward is fused as well.
+FUSED_CHAIN_IN_TRAINING = False
+
+
+def _chain_supported(mlp):
+    from . import fused_chain
+    return fused_chain._supported(mlp)
+
+
 class _NoCtx:
     """Stand-in for the autograd context when the encode runs without gradient tracking."""
     needs_input_grad = (False,) * 6
@@ -286,7 +299,19 @@ class NeuralRGB(torch.nn.Module):
             input_list = [t for t in input_list if t is not view_enc]
         if self.cfg_rgb.mode == "no_normal":
             input_list = [t for t in input_list if t is not normals]
-        return self.mlp(torch.cat(input_list, dim=-1)).sigmoid()
+        input_vec = torch.cat(input_list, dim=-1)
+        if input_vec.is_cuda and _chain_supported(self.mlp):
+            # tcgen05 chain kernel (csrc/mlp_chain.cu): all five layers + sigmoid in one launch
+            from . import fused_chain
+            flat = input_vec.reshape(-1, input_vec.shape[-1]).float().contiguous()
+            needs_graph = torch.is_grad_enabled() and (flat.requires_grad or any(p.requires_grad for p in self.mlp.parameters()))
+            if not needs_graph:
+                out = fused_chain.mlp_forward(self.mlp, flat, final_act="sigmoid")
+                return out.view(*input_vec.shape[:-1], out.shape[-1])
+            if FUSED_CHAIN_IN_TRAINING:
+                out = fused_chain.fused_mlp(self.mlp, flat, final_act="sigmoid")
+                return out.view(*input_vec.shape[:-1], out.shape[-1])
+        return self.mlp(input_vec).sigmoid()
 
     def encode_view(self, rays_unit):
         if self.cfg_rgb.encoding_view.type == "fourier":
@@ -331,6 +356,22 @@ class BackgroundNeRF(torch.nn.Module):
 
     def forward(self, points_3D, rays_unit, app_outside):
         points_enc = self.encode(points_3D)
+        fused = points_enc.is_cuda and app_outside is None and self.cfg_background.view_dep and \
+            _chain_supported(self.mlp_feat) and _chain_supported(self.mlp_rgb)
+        if fused:
+            from . import fused_chain
+            lead = points_enc.shape[:-1]
+            enc = points_enc.reshape(-1, points_enc.shape[-1]).float().contiguous()
+            venc = self.encode_view(rays_unit).reshape(enc.shape[0], -1).float().contiguous()
+            needs_graph = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+            if not needs_graph:   # whole network (both MLPs, density, sigmoid) in ONE launch
+                rgb, density = fused_chain.background_forward(self, enc, venc)
+                return rgb.view(*lead, 3), density.view(*lead)
+            if FUSED_CHAIN_IN_TRAINING:
+                out = fused_chain.fused_mlp(self.mlp_feat, enc, final_act="none")
+                density, feat = self.activ_density(out[..., 0]), self.mlp_feat.activ(out[..., 1:])
+                rgb = fused_chain.fused_mlp(self.mlp_rgb, torch.cat([feat, venc], dim=-1), final_act="sigmoid")
+                return rgb.view(*lead, 3), density.view(*lead)
         out = self.mlp_feat(points_enc)
         density, feat = self.activ_density(out[..., 0]), self.mlp_feat.activ(out[..., 1:])
         if not self.cfg_background.view_dep:

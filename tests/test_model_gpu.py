@@ -137,3 +137,30 @@ def test_textured_mesh_extraction_with_the_model(na_lib, cuda_device, golden_dir
     assert len(m.vertices) > 100 and m.faces.max() < len(m.vertices)
     assert m.visual.vertex_colors.shape == (len(m.vertices), 4) and m.visual.vertex_colors.dtype == np.uint8
     assert np.linalg.norm(m.vertices, axis=1).max() < 1.0          # bounding-sphere filter (mesh.py:136-148)
+
+
+def test_fused_chain_in_training_matches_library_path(na_lib, cuda_device, golden_dir):
+    """Opt-in: colour + background networks through the tcgen05 chain kernel with autograd -- same loss gradients."""
+    from neuralangelo_b200 import modules
+    G = _load(golden_dir, 6)
+    d = cuda_device
+    pts = (torch.rand(1, 40, 6, 3, generator=torch.Generator().manual_seed(1)) * 1.6 - 0.8).to(d)
+    rays = torch.nn.functional.normalize(torch.randn(1, 40, 6, 3, generator=torch.Generator().manual_seed(2)), dim=-1).to(d)
+    grads = {}
+    for flag in (False, True):
+        modules.FUSED_CHAIN_IN_TRAINING = flag
+        try:
+            model = _build(G, 6, d)
+            rgb, dens = model.background_nerf(pts * 3.0, rays, None)
+            normals = torch.nn.functional.normalize(
+                torch.randn(pts.shape, device=d, generator=torch.Generator(device=d).manual_seed(4)), dim=-1)
+            feats = torch.rand(1, 40, 6, 64, device=d, generator=torch.Generator(device=d).manual_seed(3))
+            rgb2 = model.neural_rgb(pts, normals, rays, feats, app=None)
+            (rgb.sum() + dens.sum() + (rgb2 ** 2).sum()).backward()
+            grads[flag] = {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}
+        finally:
+            modules.FUSED_CHAIN_IN_TRAINING = False
+    assert grads[True].keys() == grads[False].keys() and len(grads[True]) > 10
+    for k in grads[True]:
+        ref = grads[False][k]
+        assert (grads[True][k] - ref).norm().item() <= 1e-4 * max(ref.norm().item(), 1e-12), k
