@@ -249,8 +249,10 @@ def run_ours(args, rank, local_rank, world):
         elapsed_ms, e2e_ms = t.tolist()
     del out, dout, dtable, table, pts_dev
     torch.cuda.empty_cache()
-    extras = {} if args.no_extras else collect_extras(args, rank, world, dev)
     if rank != 0:
+        if not args.no_extras:
+            with Watchdog(args.extras_timeout, None):
+                collect_extras(args, rank, world, dev)
         return
     ms_per_step = elapsed_ms / args.steps
     step_bytes = (fwd_bytes + bwd_bytes) * world
@@ -279,7 +281,6 @@ def run_ours(args, rank, local_rank, world):
                      "other_kernels": {"hashgrid_taps_fwd_kernel": {"ms": fwd_ms, "GBps": fwd_bytes / fwd_ms / 1e6},
                                        "hashgrid_taps_bwd_kernel": {"ms": bwd_ms, "GBps": bwd_bytes / bwd_ms / 1e6}}},
     }
-    line["extras"] = extras
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
         n_sample = 1 << 17
@@ -412,6 +413,7 @@ def main():
     ap.add_argument("--workload", default="encode", choices=["encode"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the secondary train-step / mesh measurements")
+    ap.add_argument("--extras-timeout", type=float, default=240.0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", 0))
