@@ -61,6 +61,29 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
 
 
+class Watchdog:
+    """If the guarded block does not finish in `seconds`, print the pending JSON line (rank 0) and leave the process."""
+
+    def __init__(self, seconds, line):
+        self.seconds, self.line = seconds, line
+
+    def _fire(self):
+        if self.line is not None:
+            self.line["extras"] = {"error": f"extras did not finish within {self.seconds} s"}
+            print(json.dumps(self.line), flush=True)
+        os._exit(0)
+
+    def __enter__(self):
+        self.timer = threading.Timer(self.seconds, self._fire)
+        self.timer.daemon = True
+        self.timer.start()
+        return self
+
+    def __exit__(self, *exc):
+        self.timer.cancel()
+        return False
+
+
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
     FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -288,6 +311,12 @@ def run_ours(args, rank, local_rank, world):
         line["cpu_baseline"] = {"value": gbps, "unit": "GB/s", "cores": threads, "kind": "port",
                                 "sample": f"{n_sample} of {N_POINTS} points x 7 taps fwd+bwd once ({dt:.1f} s), full "
                                           "1.46 GB table; GB/s = full-size algorithmic bytes x (sample/full) / seconds"}
+    # secondary measurements last, under a watchdog: whatever happens there (a hung collective included), the
+    # headline line is printed exactly once
+    line["extras"] = {}
+    if not args.no_extras:
+        with Watchdog(args.extras_timeout, line):
+            line["extras"] = collect_extras(args, rank, world, dev)
     print(json.dumps(line), flush=True)
 
 
