@@ -443,6 +443,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the secondary train-step / mesh measurements")
     ap.add_argument("--extras-timeout", type=float, default=240.0)
+    ap.add_argument("--run-timeout", type=float, default=540.0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", 0))
@@ -451,13 +452,25 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
+    # whole-run guard: a rank that never shows up (or a wedged collective) must not hang the launch for ever
+    def _give_up():
+        if rank == 0:
+            print(json.dumps({"metric": "hashgrid_encode_fwd_bwd_algorithmic_GBps", "value": None, "unit": "GB/s",
+                              "n_gpus": world, "error": f"bench.py did not finish within {args.run_timeout} s"}), flush=True)
+        os._exit(3)
+    guard = threading.Timer(args.run_timeout, _give_up)
+    guard.daemon = True
+    guard.start()
     if world > 1:
+        import datetime
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         torch.cuda.set_device(local_rank)
-        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank),
+                                             timeout=datetime.timedelta(seconds=180))
     try:
         run_ours(args, rank, local_rank, world)
     finally:
+        guard.cancel()
         if world > 1:
             torch.distributed.destroy_process_group()
 
