@@ -421,8 +421,26 @@ def extra_mesh(rank, world, dev, res=512):
     return out
 
 
+def extra_cpu_path():
+    """BASELINE.json configs[0] on the host cores (reported baseline, not a target): the CPU restatement of the
+    reference's own CPU-runnable path -- Fourier-encoded NeuralSDF, 1024 rays x (64 + 32) samples forward + backward,
+    then extract_mesh at resolution 256 / block 128 with the serial C marching cubes (oracle/cpu_path.py, pinned to
+    the reference by tests/test_oracle_cpu_path.py)."""
+    from oracle import cpu_path   # CPU baseline leg
+    threads = os.cpu_count() or 1
+    out = cpu_path.timed_baseline(n_rays=1024, resolution=256, threads=threads)
+    out["kind"] = "port"
+    out["cores"] = threads
+    return out
+
+
 def collect_extras(args, rank, world, dev):
     extras = {}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            extras["cpu_path_configs0"] = extra_cpu_path()
+        except Exception as e:  # noqa: BLE001
+            extras["cpu_path_configs0"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     for name, fn in (("train_step", lambda: extra_train_step(rank, world, dev)),
                      ("train_step_4_active_levels", lambda: extra_train_step(rank, world, dev, force_all_levels=False)),
                      ("mesh_extract", lambda: extra_mesh(rank, world, dev))):

@@ -187,7 +187,49 @@ def model_fixtures():
               "table grad nnz", int((model.neural_sdf.tcnn_encoding.params.grad != 0).sum()))
 
 
+def cpu_path_fixtures():
+    """BASELINE.json configs[0] shape (Fourier-encoded NeuralSDF, no background, 6-tap gradients) on the UNMODIFIED
+    reference model, 64-wide MLPs to keep the fixture small: state dict, rays, outputs, loss, parameter gradients."""
+    reference_shim.install()
+    from neuralangelo_b200.config import AttrDict
+    from projects.neuralangelo.model import Model
+    from projects.neuralangelo.utils.misc import eikonal_loss, curvature_loss
+    torch.manual_seed(7)
+    cfg = small_model_config(6)
+    cfg.object.sdf.encoding = AttrDict(type="fourier", levels=6, coarse2fine=dict(enabled=False, init_active_level=4, step=5000))
+    cfg.background.enabled = False
+    cfg.render.num_samples = AttrDict(coarse=16, fine=4, background=0)
+    model = Model(cfg, AttrDict(num_images=None, train=dict(image_size=[20, 24]), val=dict(image_size=[10, 12])))
+    with torch.no_grad():   # give the positional-encoding columns some weight so that they matter
+        lin0 = model.neural_sdf.mlp.linears[0]
+        lin0.weight_v[:, 3:] = torch.randn_like(lin0.weight_v[:, 3:]) * 0.02
+    model.train()
+    model.neural_sdf.normal_eps = 1.0 / 2048      # set by hand: set_normal_epsilon needs hash-grid resolutions (modules.py:102-107)
+    model.progress = 0.03
+    g = torch.Generator().manual_seed(5)
+    R = 40
+    d = torch.randn(1, R, 3, generator=g) * 0.15 + torch.tensor([0.0, 0.0, 1.0])
+    d[0, :3] = torch.tensor([0.9, 0.1, 0.3])      # rays that miss the unit sphere
+    ray = torch.nn.functional.normalize(d, dim=-1)
+    center = torch.tensor([0.0, 0.0, -3.0]).expand(1, R, 3).contiguous()
+    target = torch.rand(1, R, 3, generator=g)
+    out = model.render_rays(center, ray, sample_idx=torch.arange(1), stratified=False)
+    loss = 3 * torch.nn.functional.l1_loss(out["rgb"], target) + 0.1 * eikonal_loss(out["gradients"], out["outside"]) \
+        + 5e-4 * curvature_loss(out["hessians"], out["outside"])
+    loss.backward()
+    fx = {"in_center": _np(center), "in_ray": _np(ray), "in_target": _np(target), "loss": _np(loss)}
+    for k in ("rgb", "dists", "weights", "gradients", "hessians", "outside"):
+        fx["out_" + k] = _np(out[k])
+    for k, v in model.state_dict().items():
+        fx["sd_" + k] = _np(v)
+    for k, p in model.named_parameters():
+        fx["grad_" + k] = _np(p.grad) if p.grad is not None else np.zeros(0, dtype=np.float32)
+    np.savez_compressed(os.path.join(OUT, "cpu_path_golden.npz"), **fx)
+    print(f"wrote cpu_path_golden.npz: loss {float(loss):.6f}, outside rays {int(out['outside'].sum())}")
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     render_fixtures()
     model_fixtures()
+    cpu_path_fixtures()

@@ -1,0 +1,57 @@
+"""CPU: the C-ABI library loads, exports every entry point that include/na_b200.h declares, and the ctypes
+binding covers all of them (no compute calls: there is no GPU here)."""
+import ctypes
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_entry_points():
+    text = open(os.path.join(ROOT, "include", "na_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(na_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_declares_the_expected_surface():
+    names = declared_entry_points()
+    for must in ("na_hashgrid_fwd", "na_hashgrid_bwd", "na_hashgrid_taps_fwd", "na_hashgrid_taps_bwd", "na_sdf_mlp_fwd",
+                 "na_sdf_mlp_bwd", "na_mlp_chain_fwd", "na_neus_render_fwd", "na_neus_render_bwd", "na_alpha_weights_fwd",
+                 "na_sample_pdf", "na_neus_upsample", "na_merge_sorted", "na_mc_count", "na_mc_emit", "na_adamw_step",
+                 "na_last_error", "na_abi_version"):
+        assert must in names, must
+
+
+def test_library_exports_every_declared_symbol(na_lib):
+    from neuralangelo_b200 import _lib
+    raw = ctypes.CDLL(_lib.LIB_PATH)
+    missing = [n for n in declared_entry_points() if not hasattr(raw, n)]
+    assert not missing, f"declared in include/na_b200.h but not exported: {missing}"
+
+
+def test_ctypes_binding_covers_every_declared_symbol(na_lib):
+    from neuralangelo_b200 import _lib
+    bound = set(_lib.exported_signatures())
+    unbound = [n for n in declared_entry_points() if n not in bound]
+    assert not unbound, f"declared but not bound in neuralangelo_b200/_lib.py: {unbound}"
+
+
+def test_abi_version_and_error_string(na_lib):
+    assert na_lib.na_abi_version() >= 1
+    assert isinstance(na_lib.na_last_error(), bytes)
+    # host-only entry point: argument validation without a GPU
+    from neuralangelo_b200 import _lib
+    desc = _lib.HashGridDesc()
+    assert na_lib.na_hashgrid_make_desc(64, 8, 22, 32, 1.3, ctypes.byref(desc)) == -1
+    assert b"n_levels" in na_lib.na_last_error()
+    assert na_lib.na_mc_scratch_bytes(129, 129, 129) > 128 ** 3 * 5
+    assert na_lib.na_mc_static_max_cells() == 64 ** 3
+
+
+def test_product_refuses_cpu_tensors(na_lib):
+    """No CPU fallback: the wrappers raise instead of computing on the host."""
+    import pytest
+    import torch
+    from neuralangelo_b200 import _lib, render
+    with pytest.raises(_lib.NaError):
+        render.alpha_compositing_weights(torch.rand(1, 2, 3))
