@@ -311,7 +311,7 @@ hashgrid_taps_fwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
 // backward: scatter-add into the table gradient (same mapping; grid.y covers active levels only)
 // ---------------------------------------------------------------------------------------------
 template <int F, bool ALIGNED>
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(kThreads, 2)
 hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ x,
                          int64_t n_points, na_unit_map map, uint32_t active_levels,
                          const __grid_constant__ TapParams taps, const float* __restrict__ dout,
@@ -333,31 +333,53 @@ hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
     const int64_t cta_base = (int64_t)blockIdx.x * m.points_per_cta;
     const int step = (kThreads / 32) * m.points_per_warp;
 
-    for (int i = warp * m.points_per_warp + pt_in_warp; i < m.points_per_cta; i += step) {
+    // Software pipeline over the CTA's points: the coordinates and all taps' upstream gradients of point i+1 are
+    // requested before point i is processed, so two points' worth of loads are in flight per lane (the kernel is
+    // bound by memory latency at two CTAs per SM, not by bytes: profiles/r01_hashgrid_planes_ncu_summary.md).
+    float nx0 = 0.f, nx1 = 0.f, nx2 = 0.f;
+    float4 ndv[kMaxTaps];
+    auto prefetch = [&](int i) {
+        const int64_t n = cta_base + i;
+        const bool ok = i < m.points_per_cta && n < n_points;
+#pragma unroll
+        for (int t = 0; t < kMaxTaps; ++t) ndv[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok) {
+            nx0 = __ldg(x + n * 3 + 0), nx1 = __ldg(x + n * 3 + 1), nx2 = __ldg(x + n * 3 + 2);
+            const float* gn = dout + n * dout_stride + level * dout_level_stride + sub * S::V;
+#pragma unroll
+            for (int t = 0; t < kMaxTaps; ++t)
+                if ((uint32_t)t < taps.n) ndv[t] = VT::template load_stream_hint<ALIGNED>(gn + t * dout_tap_stride, stream);
+        }
+    };
+    const int i0 = warp * m.points_per_warp + pt_in_warp;
+    prefetch(i0);
+    for (int i = i0; i < m.points_per_cta; i += step) {
         const int64_t n = cta_base + i;
         if (n >= n_points) break;
         const float* g = dout + n * dout_stride + level * dout_level_stride + sub * S::V;
-        const float x0 = __ldg(x + n * 3 + 0), x1 = __ldg(x + n * 3 + 1), x2 = __ldg(x + n * 3 + 2);
+        const float x0 = nx0, x1 = nx1, x2 = nx2;
+        float4 dv[kMaxTaps];
+#pragma unroll
+        for (int t = 0; t < kMaxTaps; ++t) dv[t] = ndv[t];
+        prefetch(i + step);
         const Cell c0 = locate_tap(L, map, taps, 0, x0, x1, x2);
         float4 acc[8];
-        {
-            const float4 d = VT::template load_stream_hint<ALIGNED>(g, stream);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const float w = corner_weight(c0, k);
-                acc[k] = make_float4(w * d.x, w * d.y, w * d.z, w * d.w);
-            }
+        for (int k = 0; k < 8; ++k) {
+            const float w = corner_weight(c0, k);
+            acc[k] = make_float4(w * dv[0].x, w * dv[0].y, w * dv[0].z, w * dv[0].w);
         }
         uint32_t pending = 0;
-#pragma unroll 1
-        for (uint32_t t = 1; t < taps.n; ++t) {
-            const Cell c = locate_tap(L, map, taps, t, x0, x1, x2);
-            if (same_cell(c, c0)) {  // pre-sum: one reduction per corner for all taps of this cell
-                const float4 d = VT::template load_stream_hint<ALIGNED>(g + t * dout_tap_stride, stream);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) axpy4(acc[k], corner_weight(c, k), d);
-            } else {
-                pending |= 1u << t;
+        for (int t = 1; t < kMaxTaps; ++t) {
+            if ((uint32_t)t < taps.n) {
+                const Cell c = locate_tap(L, map, taps, t, x0, x1, x2);
+                if (same_cell(c, c0)) {  // pre-sum: one reduction per corner for all taps of this cell
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) axpy4(acc[k], corner_weight(c, k), dv[t]);
+                } else {
+                    pending |= 1u << t;
+                }
             }
         }
 #pragma unroll
