@@ -69,13 +69,21 @@ struct MlpParams {
 };
 
 // ---------------------------------------------------------------- the kernel
-__global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_constant__ MlpParams P) {
+// The forward kernel runs 16 compute warps (four column groups x four TMEM lane quarters): its time is the softplus /
+// split epilogue, and four warps per scheduler hide the MUFU / TMEM-load latencies that two could not.
+constexpr int kFwdWarps = 16;
+constexpr int kFwdCompute = kFwdWarps * 32;
+constexpr int kFwdThreads = kFwdCompute + 64;
+constexpr int kFwdGroups = kFwdWarps / 4;
+constexpr int kFwdSmemBytes = kSmemBytes + 2 * kTileM * 4;   // head partials for four column groups
+
+__global__ void __launch_bounds__(kFwdThreads, 1) sdf_mlp_fwd_kernel(const __grid_constant__ MlpParams P) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* a_hi = smem;
     uint8_t* a_lo = smem + kABytes;
     uint8_t* b_ring = smem + 2 * kABytes;
-    float* head_partial = reinterpret_cast<float*>(b_ring + kStages * kBStageBytes);  // [2][kTileM]
-    float* s_bias = head_partial + 2 * kTileM;   // [2][kMaxN] per-layer biases
+    float* head_partial = reinterpret_cast<float*>(b_ring + kStages * kBStageBytes);  // [kFwdGroups][kTileM]
+    float* s_bias = head_partial + kFwdGroups * kTileM;   // [2][kMaxN] per-layer biases
     float* s_head = s_bias + 2 * kMaxN;           // [kMaxN] SDF head weights
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_head + kMaxN);
     // bars: [0,S) b_full, [S,2S) b_empty, 2S a_ready, 2S+1 d_ready; then the TMEM base address word
@@ -89,7 +97,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
     const int n = P.n;
     const int64_t n_tiles = (P.m + kTileM - 1) / kTileM;
 
-    for (int i = threadIdx.x; i < n; i += kThreads) {
+    for (int i = threadIdx.x; i < n; i += kFwdThreads) {
         s_bias[i] = P.layer[0].bias[i];
         s_bias[kMaxN + i] = P.n_layers > 1 ? P.layer[1].bias[i] : 0.f;
         s_head[i] = P.w_head ? P.w_head[i] : 0.f;
@@ -99,11 +107,11 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
             mbar_init(b_full(s), 1);
             mbar_init(b_empty(s), 1);
         }
-        mbar_init(a_ready, kComputeThreads);
+        mbar_init(a_ready, kFwdCompute);
         mbar_init(d_ready, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == kComputeWarps) {  // MMA warp owns the TMEM allocation: D_main [0,256) and D_cross [256,512)
+    if (warp == kFwdWarps) {  // MMA warp owns the TMEM allocation: D_main [0,256) and D_cross [256,512)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                      "r"(512u)
                      : "memory");
@@ -115,7 +123,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t d_main = tmem_base, d_cross = tmem_base + 256;
 
-    if (warp == kComputeWarps + 1) {
+    if (warp == kFwdWarps + 1) {
         // ===================== weight loader =====================
         if (lane == 0) {
             uint32_t it = 0;
@@ -141,7 +149,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
                 }
             }
         }
-    } else if (warp == kComputeWarps) {
+    } else if (warp == kFwdWarps) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
             const uint32_t idesc = make_idesc(kTileM, n);
@@ -182,7 +190,9 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
         // ===================== compute warps =====================
         const int tid = threadIdx.x;                // 0..255
         const int quarter = warp & 3;               // TMEM lane quarter this warp may access
-        const int half = warp >> 2;                 // which half of the N columns this warp handles
+        const int group = warp >> 2;                // which slice of the N columns this warp handles
+        const int cols_per_group = n / kFwdGroups >= 32 ? n / kFwdGroups : 32;
+        const int n_groups = n / cols_per_group;    // narrow layers leave the last groups without columns
         const int row = quarter * 32 + lane;        // accumulator row == TMEM lane
         const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
         uint32_t layer_it = 0;
@@ -194,13 +204,13 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
             {
                 const int chunks = P.layer[0].k_pad / 8;
                 const int total = kTileM * chunks;
-                constexpr int kPerThread = kTileM * (kMaxK / 8) / kComputeThreads;  // 16
+                constexpr int kPerThread = kTileM * (kMaxK / 8) / kFwdCompute;  // 8
 #pragma unroll 1
                 for (int base = 0; base < kPerThread; base += 4) {
                     float v[4][8];
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        const int idx = (base + u) * kComputeThreads + tid;
+                        const int idx = (base + u) * kFwdCompute + tid;
                         const int r = idx / chunks, kc = idx - r * chunks;
                         const int64_t gr = row0 + r;
                         const float* src = P.x + gr * P.ldx + kc * 8;
@@ -210,7 +220,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
                     }
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        const int idx = (base + u) * kComputeThreads + tid;
+                        const int idx = (base + u) * kFwdCompute + tid;
                         if (idx >= total) continue;
                         const int r = idx / chunks, kc = idx - r * chunks;
                         uint32_t hi[4], lo[4];
@@ -238,22 +248,23 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
                 const float* bias = s_bias + l * kMaxN;
                 const float inv_beta = 1.f / P.beta;
                 float dot = 0.f;
-                const int col_begin = half * (n / 2), col_end = col_begin + n / 2;
-                for (int c0 = col_begin; c0 < col_end; c0 += 32) {
-                    uint32_t rm[32], rc[32];
-                    tc_ld32(d_main + lane_addr + c0, rm);
-                    tc_ld32(d_cross + lane_addr + c0, rc);
+                const int col_begin = group < n_groups ? group * cols_per_group : 0;
+                const int col_end = group < n_groups ? col_begin + cols_per_group : 0;
+                for (int c0 = col_begin; c0 < col_end; c0 += 16) {
+                    uint32_t rm[16], rc[16];
+                    tc_ld16(d_main + lane_addr + c0, rm);
+                    tc_ld16(d_cross + lane_addr + c0, rc);
                     tc_wait_ld();
-                    float act[32];
+                    float act[16];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
+                    for (int j = 0; j < 16; ++j) {
                         const float pre = fmaf(__uint_as_float(rc[j]), kLoInv, __uint_as_float(rm[j])) + bias[c0 + j];
                         act[j] = softplus(pre, P.beta, inv_beta);
                         if (head) dot = fmaf(act[j], s_head[c0 + j], dot);
                     }
                     if (!last) {  // next layer's A operand, straight back to shared memory
 #pragma unroll
-                        for (int q = 0; q < 4; ++q) {
+                        for (int q = 0; q < 2; ++q) {
                             uint32_t hi[4], lo[4];
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
@@ -272,16 +283,20 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
                     if (l == 0 && P.hidden_out) dst = P.hidden_out + (row0 + row) * P.ld_hidden + c0;
                     if (dst && row0 + row < P.m) {
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4)
+                        for (int j = 0; j < 16; j += 4)
                             *reinterpret_cast<float4*>(dst + j) = make_float4(act[j], act[j + 1], act[j + 2], act[j + 3]);
                     }
                 }
                 if (head) {
-                    head_partial[half * kTileM + row] = dot;
-                    asm volatile("bar.sync 1, %0;" ::"n"(kComputeThreads) : "memory");
-                    if (half == 0 && row0 + row < P.m && P.sdf_out)
-                        P.sdf_out[row0 + row] = head_partial[row] + head_partial[kTileM + row] + __ldg(P.b_head);
-                    asm volatile("bar.sync 1, %0;" ::"n"(kComputeThreads) : "memory");
+                    head_partial[group * kTileM + row] = dot;    // groups without columns contribute 0
+                    asm volatile("bar.sync 1, %0;" ::"n"(kFwdCompute) : "memory");
+                    if (group == 0 && row0 + row < P.m && P.sdf_out) {
+                        float sum = __ldg(P.b_head);
+#pragma unroll
+                        for (int gi = 0; gi < kFwdGroups; ++gi) sum += head_partial[gi * kTileM + row];
+                        P.sdf_out[row0 + row] = sum;
+                    }
+                    asm volatile("bar.sync 1, %0;" ::"n"(kFwdCompute) : "memory");
                 }
                 tc_fence_before();
                 if (!last) {
@@ -296,7 +311,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_fwd_kernel(const __grid_c
 
     tc_fence_before();
     __syncthreads();
-    if (warp == kComputeWarps) {
+    if (warp == kFwdWarps) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
     }
@@ -602,12 +617,12 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_c
 
 // The opt-in to > 48 KB of dynamic shared memory is per device and is not a stream operation: do it once per
 // (kernel, device) so that later launches -- possibly under CUDA-graph capture -- make no attribute call.
-int ensure_smem_attr(int which, const void* func, const char* what) {
+int ensure_smem_attr(int which, const void* func, const char* what, int smem_bytes) {
     static bool done[2][64] = {};
     int dev = 0;
     if (int rc = na::check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return rc;
     if (dev < 0 || dev >= 64 || !done[which][dev]) {
-        if (int rc = na::check_cuda(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes),
+        if (int rc = na::check_cuda(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes),
                                     what))
             return rc;
         if (dev >= 0 && dev < 64) done[which][dev] = true;
@@ -644,10 +659,10 @@ extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, in
     P.layer[1] = Layer{(const __half*)w1_hi, (const __half*)w1_lo, b1, n};
     P.w_head = w_head, P.b_head = b_head, P.beta = beta;
     P.sdf_out = sdf_out, P.feat_out = feat_out, P.ld_feat = ld_feat, P.hidden_out = hidden_out, P.ld_hidden = ld_hidden;
-    if (int rc = ensure_smem_attr(0, (const void*)sdf_mlp_fwd_kernel, "cudaFuncSetAttribute(sdf_mlp_fwd_kernel)")) return rc;
+    if (int rc = ensure_smem_attr(0, (const void*)sdf_mlp_fwd_kernel, "cudaFuncSetAttribute(sdf_mlp_fwd_kernel)", kFwdSmemBytes)) return rc;
     const int64_t tiles = (m + kTileM - 1) / kTileM;
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
-    sdf_mlp_fwd_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);
+    sdf_mlp_fwd_kernel<<<grid, kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(P);
     NA_CHECK_LAUNCH("sdf_mlp_fwd_kernel");
     return NA_OK;
 }
@@ -676,7 +691,7 @@ extern "C" int na_sdf_mlp_bwd(int64_t m, int n, int k0, int k0_pad, int two_laye
     P.w0t = Layer{(const __half*)w0t_hi, (const __half*)w0t_lo, nullptr, n};
     P.w_head = w_head, P.beta = beta, P.norms = norms;
     P.dz1 = dz1, P.dz0 = dz0, P.dx = dx, P.ld_dx = ld_dx;
-    if (int rc = ensure_smem_attr(1, (const void*)sdf_mlp_bwd_kernel, "cudaFuncSetAttribute(sdf_mlp_bwd_kernel)")) return rc;
+    if (int rc = ensure_smem_attr(1, (const void*)sdf_mlp_bwd_kernel, "cudaFuncSetAttribute(sdf_mlp_bwd_kernel)", kSmemBytes)) return rc;
     const int64_t tiles = (m + kTileM - 1) / kTileM;
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
     sdf_mlp_bwd_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);
