@@ -26,6 +26,7 @@
 // so a thread that owns one row writes its eight-column chunks with conflict-free 16-byte stores and the
 // host packs the weights once per optimiser step into the exact shared-memory image.
 #include "tc_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -312,6 +313,294 @@ __global__ void __launch_bounds__(kFwdThreads, 1) sdf_mlp_fwd_kernel(const __gri
     tc_fence_before();
     __syncthreads();
     if (warp == kFwdWarps) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+
+// ==================================================================================================
+// Pipelined form of the forward for the SDF-only evaluation (n_layers == 1: finite-difference taps, the no-grad
+// evaluations of the hierarchical sampler, the lattice queries of the mesh extractor -- four fifths of all point
+// evaluations).  The kernel above runs input staging, MMA and epilogue of a tile one after the other; here they
+// overlap:
+//   * input loader (warp 18): ONE bulk copy (cp.async.bulk) per tile brings the raw fp32 rows -- contiguous in HBM
+//     when the rows are packed -- into a staging buffer while the previous tile is being processed;
+//   * compute warps 0-15: convert the staged rows shared->shared into the split-fp16 A image, then run the
+//     epilogues;
+//   * the N columns are processed as two halves ("units"), each with its own D_main / D_cross accumulator pair
+//     (2 x 256 TMEM columns), so the MMAs of one unit run under the epilogue of the other;
+//   * weight loader (warp 17): streams the matching N-half of W_hi / W_lo through a 4-stage ring of 32-wide K blocks.
+// Barriers (one completion per tile each, parity = local tile index & 1):
+//   raw_full / raw_empty   staging buffer:   input loader <-> compute warps
+//   a_ready / a_free       A image:          compute warps <-> MMA warp (a_free = tcgen05.commit after the 2nd unit)
+//   d_full[h] / d_empty[h] accumulators:     MMA warp <-> compute warps
+// Requirements checked by the host entry point: packed rows (ldx == k0) starting 16-byte aligned, odd k0 (conflict-
+// free column walks of the staging buffer; 3 + levels * features is always odd), hidden width 128 or 256.
+// ==================================================================================================
+constexpr int kPipeWarps = 16;
+constexpr int kPipeCompute = kPipeWarps * 32;
+constexpr int kPipeThreads = kPipeCompute + 96;   // + MMA warp, weight loader, input loader
+constexpr int kPipeStages = 4;
+constexpr int kPipeBlockK = 32;                   // K elements per ring stage (two UMMA k-steps)
+constexpr int kPipeBars = 2 * kPipeStages + 8;
+
+__host__ __device__ inline uint32_t pipe_raw_bytes(int k0) { return ((uint32_t)kTileM * k0 * 4 + 127u) & ~127u; }
+__host__ __device__ inline uint32_t pipe_stage_bytes(int n) { return 2u * (kPipeBlockK / 8) * (uint32_t)(n / 2) * 16u; }
+__host__ __device__ inline uint32_t pipe_smem_bytes(int k0, int k_pad, int n) {
+    return 2u * kTileM * k_pad * 2u + pipe_raw_bytes(k0) + kPipeStages * pipe_stage_bytes(n) +
+           (2u * 4u * kTileM + 2u * kMaxN) * 4u + kPipeBars * 8u + 16u;
+}
+
+__global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(const __grid_constant__ MlpParams P) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int n = P.n, nh = n / 2, k0 = P.k0, k_pad = P.layer[0].k_pad;
+    const int chunks = k_pad / 8;
+    const uint32_t a_bytes = (uint32_t)kTileM * k_pad * 2;
+    const uint32_t chunk_bytes = (uint32_t)nh * 16;                     // one 8-wide k-chunk of one N half
+    const uint32_t stage_half = (kPipeBlockK / 8) * chunk_bytes;        // the W_hi (or W_lo) part of a ring stage
+    uint8_t* a_hi = smem;
+    uint8_t* a_lo = a_hi + a_bytes;
+    uint8_t* raw = a_lo + a_bytes;
+    uint8_t* b_ring = raw + pipe_raw_bytes(k0);
+    float* head_partial = reinterpret_cast<float*>(b_ring + kPipeStages * 2 * stage_half);   // [2][4][kTileM]
+    float* s_bias = head_partial + 2 * 4 * kTileM;
+    float* s_head = s_bias + kMaxN;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_head + kMaxN);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kPipeBars);
+    const uint32_t bar0 = smem_u32(bars);
+    auto b_full = [&](int s) { return bar0 + 8u * s; };
+    auto b_empty = [&](int s) { return bar0 + 8u * (kPipeStages + s); };
+    const uint32_t raw_full = bar0 + 8u * (2 * kPipeStages), raw_empty = raw_full + 8u, a_ready = raw_full + 16u,
+                   a_free = raw_full + 24u;
+    auto d_full = [&](int h) { return raw_full + 32u + 8u * h; };
+    auto d_empty = [&](int h) { return raw_full + 48u + 8u * h; };
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t n_tiles = (P.m + kTileM - 1) / kTileM;
+    const bool head = P.w_head != nullptr;
+
+    for (int i = threadIdx.x; i < n; i += kPipeThreads) {
+        s_bias[i] = P.layer[0].bias[i];
+        s_head[i] = head ? P.w_head[i] : 0.f;
+    }
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kPipeStages; ++s) {
+            mbar_init(b_full(s), 1);
+            mbar_init(b_empty(s), 1);
+        }
+        mbar_init(raw_full, 1);
+        mbar_init(raw_empty, kPipeCompute);
+        mbar_init(a_ready, kPipeCompute);
+        mbar_init(a_free, 1);
+        for (int h = 0; h < 2; ++h) {
+            mbar_init(d_full(h), 1);
+            mbar_init(d_empty(h), kPipeCompute);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == kPipeWarps) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;   // unit h: D_main at columns [256 h, 256 h + nh), D_cross at + 128
+
+    if (warp == kPipeWarps + 2) {
+        // ===================== input loader =====================
+        if (lane == 0) {
+            auto issue = [&](int64_t tile) {
+                const int64_t row0 = tile * kTileM;
+                const int rows = (int)(P.m - row0 < kTileM ? P.m - row0 : kTileM);
+                const float* src = P.x + row0 * k0;
+                const uint32_t bytes = (uint32_t)rows * k0 * 4, bulk = bytes & ~15u;
+                float* rawf = reinterpret_cast<float*>(raw);
+                for (uint32_t w = bulk / 4; w < bytes / 4; ++w) rawf[w] = __ldg(src + w);   // < 16-byte tail of the last tile
+                mbar_expect_tx(raw_full, bulk);
+                bulk_copy_g2s(smem_u32(raw), src, bulk, raw_full);
+            };
+            if ((int64_t)blockIdx.x < n_tiles) issue(blockIdx.x);
+            uint32_t q = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
+                mbar_wait(raw_empty, q & 1);
+                if (tile + gridDim.x < n_tiles) issue(tile + gridDim.x);
+            }
+        }
+    } else if (warp == kPipeWarps + 1) {
+        // ===================== weight loader =====================
+        if (lane == 0) {
+            const uint8_t* w_hi = reinterpret_cast<const uint8_t*>(P.layer[0].w_hi);
+            const uint8_t* w_lo = reinterpret_cast<const uint8_t*>(P.layer[0].w_lo);
+            uint32_t it = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                for (int h = 0; h < 2; ++h) {
+                    for (int c0 = 0; c0 < chunks; c0 += kPipeBlockK / 8, ++it) {
+                        const int s = it % kPipeStages;
+                        mbar_wait(b_empty(s), ((it / kPipeStages) & 1) ^ 1);
+                        const int nc = min(kPipeBlockK / 8, chunks - c0);
+                        mbar_expect_tx(b_full(s), 2u * nc * chunk_bytes);
+                        const uint32_t dst = smem_u32(b_ring + s * 2 * stage_half);
+                        for (int c = 0; c < nc; ++c) {
+                            const size_t src = (size_t)(c0 + c) * ((size_t)n * 16) + (size_t)h * chunk_bytes;
+                            bulk_copy_g2s(dst + c * chunk_bytes, w_hi + src, chunk_bytes, b_full(s));
+                            bulk_copy_g2s(dst + stage_half + c * chunk_bytes, w_lo + src, chunk_bytes, b_full(s));
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == kPipeWarps) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(kTileM, nh);
+            const uint32_t a_lbo = kTileM / 8 * 128;
+            uint32_t it = 0, q = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
+                mbar_wait(a_ready, q & 1);
+                tc_fence_after();
+                for (int h = 0; h < 2; ++h) {
+                    if (q > 0) {   // the epilogue of the previous tile has drained this accumulator pair
+                        mbar_wait(d_empty(h), (q - 1) & 1);
+                        tc_fence_after();
+                    }
+                    const uint32_t d_main = tmem_base + 256u * h, d_cross = d_main + 128u;
+                    bool first = true;
+                    for (int c0 = 0; c0 < chunks; c0 += kPipeBlockK / 8, ++it) {
+                        const int s = it % kPipeStages;
+                        mbar_wait(b_full(s), (it / kPipeStages) & 1);
+                        tc_fence_after();
+                        const int nc = min(kPipeBlockK / 8, chunks - c0);
+                        const uint32_t b_hi_addr = smem_u32(b_ring + s * 2 * stage_half);
+                        const uint32_t b_lo_addr = b_hi_addr + stage_half;
+                        for (int c = 0; c < nc; c += 2) {
+                            const uint32_t a_off = (uint32_t)(c0 + c) * a_lbo, b_off = (uint32_t)c * chunk_bytes;
+                            const uint64_t ah = make_desc(smem_u32(a_hi) + a_off, a_lbo, 128);
+                            const uint64_t al = make_desc(smem_u32(a_lo) + a_off, a_lbo, 128);
+                            const uint64_t bh = make_desc(b_hi_addr + b_off, chunk_bytes, 128);
+                            const uint64_t bl = make_desc(b_lo_addr + b_off, chunk_bytes, 128);
+                            tc_mma_f16(d_cross, al, bh, idesc, first ? 0u : 1u);
+                            tc_mma_f16(d_cross, ah, bl, idesc, 1u);
+                            tc_mma_f16(d_main, ah, bh, idesc, first ? 0u : 1u);
+                            first = false;
+                        }
+                        tc_commit(b_empty(s));
+                    }
+                    tc_commit(d_full(h));
+                }
+                tc_commit(a_free);   // every MMA that reads this tile's A image has completed
+            }
+        }
+    } else {
+        // ===================== compute warps =====================
+        const int tid = threadIdx.x;
+        const int quarter = warp & 3, group = warp >> 2;
+        const int cpg = nh / 4 >= 16 ? nh / 4 : 16;       // columns of a unit per warp group
+        const int n_groups = nh / cpg;
+        const int row = quarter * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+        const float inv_beta = 1.f / P.beta;
+        const float* rawf = reinterpret_cast<const float*>(raw);
+
+        // staged fp32 rows -> split-fp16 A image; consecutive lanes take consecutive rows: the column walk of the
+        // staging buffer has an odd word stride (k0) and the 16-byte stores are consecutive -- both conflict-free
+        auto convert = [&](int rows) {
+            const int total = kTileM * chunks;
+            for (int idx = tid; idx < total; idx += kPipeCompute) {
+                const int r = idx & (kTileM - 1), kc = idx / kTileM;
+                const float* src = rawf + r * k0 + kc * 8;
+                uint32_t hi[4], lo[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int col = kc * 8 + 2 * j;
+                    const float v0 = (r < rows && col < k0) ? src[2 * j] : 0.f;
+                    const float v1 = (r < rows && col + 1 < k0) ? src[2 * j + 1] : 0.f;
+                    __half h0, l0, h1, l1;
+                    split_f16(v0, h0, l0);
+                    split_f16(v1, h1, l1);
+                    hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                }
+                const uint32_t off = a_chunk_offset(r, kc);
+                *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            }
+        };
+        auto rows_of = [&](int64_t tile) { return (int)(P.m - tile * kTileM < kTileM ? P.m - tile * kTileM : kTileM); };
+
+        float dot = 0.f;
+        auto epilogue = [&](int h, int64_t row0) {
+            const uint32_t d_main = tmem_base + 256u * h + lane_addr, d_cross = d_main + 128u;
+            const int col_begin = group < n_groups ? group * cpg : 0;
+            const int col_end = group < n_groups ? col_begin + cpg : 0;
+            for (int c0 = col_begin; c0 < col_end; c0 += 16) {
+                uint32_t rm[16], rc[16];
+                tc_ld16(d_main + c0, rm);
+                tc_ld16(d_cross + c0, rc);
+                tc_wait_ld();
+                const int gc = h * nh + c0;   // column of the layer
+                float act[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float pre = fmaf(__uint_as_float(rc[j]), kLoInv, __uint_as_float(rm[j])) + s_bias[gc + j];
+                    act[j] = softplus(pre, P.beta, inv_beta);
+                    dot = fmaf(act[j], s_head[gc + j], dot);
+                }
+                if (P.hidden_out && row0 + row < P.m) {
+                    float* dst = P.hidden_out + (row0 + row) * P.ld_hidden + gc;
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4)
+                        *reinterpret_cast<float4*>(dst + j) = make_float4(act[j], act[j + 1], act[j + 2], act[j + 3]);
+                }
+            }
+        };
+
+        uint32_t q = 0;
+        if ((int64_t)blockIdx.x < n_tiles) {   // prologue: the first tile's A image
+            mbar_wait(raw_full, 0);
+            convert(rows_of(blockIdx.x));
+            mbar_arrive(raw_empty);
+            fence_proxy_async();
+            mbar_arrive(a_ready);
+        }
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
+            const int64_t row0 = tile * kTileM;
+            const int64_t next = tile + gridDim.x;
+            dot = 0.f;
+            mbar_wait(d_full(0), q & 1);
+            tc_fence_after();
+            epilogue(0, row0);
+            tc_fence_before();
+            mbar_arrive(d_empty(0));
+            if (next < n_tiles) {   // next tile's A image, while the second unit's MMAs / the next first unit's run
+                mbar_wait(a_free, q & 1);
+                mbar_wait(raw_full, (q + 1) & 1);
+                convert(rows_of(next));
+                mbar_arrive(raw_empty);
+                fence_proxy_async();
+                mbar_arrive(a_ready);
+            }
+            mbar_wait(d_full(1), q & 1);
+            tc_fence_after();
+            epilogue(1, row0);
+            tc_fence_before();
+            mbar_arrive(d_empty(1));
+            if (head && P.sdf_out) {
+                float* part = head_partial + (q & 1) * 4 * kTileM;
+                part[group * kTileM + row] = dot;   // groups without columns contribute 0
+                asm volatile("bar.sync 1, %0;" ::"n"(kPipeCompute) : "memory");
+                if (group == 0 && row0 + row < P.m)
+                    P.sdf_out[row0 + row] = __ldg(P.b_head) + part[row] + part[kTileM + row] + part[2 * kTileM + row] +
+                                            part[3 * kTileM + row];
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kPipeWarps) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
     }
@@ -618,7 +907,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_c
 // The opt-in to > 48 KB of dynamic shared memory is per device and is not a stream operation: do it once per
 // (kernel, device) so that later launches -- possibly under CUDA-graph capture -- make no attribute call.
 int ensure_smem_attr(int which, const void* func, const char* what, int smem_bytes) {
-    static bool done[2][64] = {};
+    static bool done[3][64] = {};
     int dev = 0;
     if (int rc = na::check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return rc;
     if (dev < 0 || dev >= 64 || !done[which][dev]) {
@@ -659,9 +948,21 @@ extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, in
     P.layer[1] = Layer{(const __half*)w1_hi, (const __half*)w1_lo, b1, n};
     P.w_head = w_head, P.b_head = b_head, P.beta = beta;
     P.sdf_out = sdf_out, P.feat_out = feat_out, P.ld_feat = ld_feat, P.hidden_out = hidden_out, P.ld_hidden = ld_hidden;
-    if (int rc = ensure_smem_attr(0, (const void*)sdf_mlp_fwd_kernel, "cudaFuncSetAttribute(sdf_mlp_fwd_kernel)", kFwdSmemBytes)) return rc;
     const int64_t tiles = (m + kTileM - 1) / kTileM;
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
+    // SDF-only evaluation of packed rows: the pipelined kernel (NA_MLP_NO_PIPE=1 is a developer switch for A/B runs)
+    static const bool no_pipe = getenv("NA_MLP_NO_PIPE") != nullptr;
+    const uint32_t pipe_smem = pipe_smem_bytes(k0, k0_pad, n);
+    if (!no_pipe && n_layers == 1 && ldx == k0 && (k0 & 1) && n % 128 == 0 && (uintptr_t)x % 16 == 0 &&
+        pipe_smem <= 227u * 1024u) {
+        if (int rc = ensure_smem_attr(2, (const void*)sdf_head_fwd_pipe_kernel,
+                                      "cudaFuncSetAttribute(sdf_head_fwd_pipe_kernel)", 227 * 1024))
+            return rc;
+        sdf_head_fwd_pipe_kernel<<<grid, kPipeThreads, pipe_smem, (cudaStream_t)stream>>>(P);
+        NA_CHECK_LAUNCH("sdf_head_fwd_pipe_kernel");
+        return NA_OK;
+    }
+    if (int rc = ensure_smem_attr(0, (const void*)sdf_mlp_fwd_kernel, "cudaFuncSetAttribute(sdf_mlp_fwd_kernel)", kFwdSmemBytes)) return rc;
     sdf_mlp_fwd_kernel<<<grid, kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(P);
     NA_CHECK_LAUNCH("sdf_mlp_fwd_kernel");
     return NA_OK;

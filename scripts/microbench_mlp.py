@@ -22,8 +22,10 @@ def timeit(fn, iters=5, warm=2):
 res = {}
 for name, wf in (("sdf_only", False), ("sdf_feat", True)):
     ms = timeit(lambda: packed.forward(x, with_sdf=True, with_feat=wf))
+    xc = x.contiguous()
+    ms_packed = timeit(lambda: packed.forward(xc, with_sdf=True, with_feat=wf))
     flop = 2 * m * (131 * 256 + 256 + (256 * 256 if wf else 0))
-    res[name] = dict(ms=ms, Mrows_s=m / ms / 1e3, fp32_equiv_TFLOPs=flop / ms / 1e9, mma_TFLOPs=3 * 2 * m * (144 * 256 + (256 * 256 if wf else 0)) / ms / 1e9)
+    res[name] = dict(ms=ms, ms_packed_rows=ms_packed, Mrows_s_packed=m / ms_packed / 1e3, Mrows_s=m / ms / 1e3, fp32_equiv_TFLOPs=flop / ms / 1e9, mma_TFLOPs=3 * 2 * m * (144 * 256 + (256 * 256 if wf else 0)) / ms / 1e9)
     with torch.no_grad():
         ms_t = timeit(lambda: mlp(x, with_sdf=True, with_feat=wf))
     res[name]["torch_fp32_ms"] = ms_t

@@ -46,6 +46,35 @@ def test_fused_sdf_mlp_forward(na_lib, cuda_device, k0, n, m):
     assert (sdf - e_sdf).abs().max().item() <= 5e-6 * max(s_scale, 1.0)
 
 
+@pytest.mark.parametrize("k0,n,m", [(131, 256, 1), (131, 256, 127), (131, 256, 130), (131, 256, 128 * 148 * 3 + 5),
+                                    (67, 128, 128 * 150 + 2), (35, 256, 1001)])
+def test_pipelined_sdf_only_forward(na_lib, cuda_device, k0, n, m):
+    """SDF-only evaluation of PACKED rows takes the pipelined kernel (bulk-copied input tiles, two accumulator
+    units): row counts that leave a < 16-byte tail (m * k0 * 4 not a multiple of 16), a single short tile, several
+    tiles per CTA.  Reference: float64 module on the CPU; and bit-equality with the staged kernel, which the same
+    entry point runs for strided rows (the arithmetic per row is the same sequence of MMAs)."""
+    from neuralangelo_b200.fused_mlp import PackedSdfMlp
+    mlp = _mlp(k0, n, seed=k0 + n + 1)
+    g = torch.Generator().manual_seed(m)
+    x = torch.randn(m, k0, generator=g) * torch.tensor([1.0] * 3 + [0.3] * (k0 - 3))
+    ref_sdf, _ = mlp.double()(x.double(), with_feat=False)
+    mlp = mlp.float().to(cuda_device)
+    packed = PackedSdfMlp(mlp, beta=100.0)
+    xp = x.to(cuda_device).contiguous()
+    guard = torch.full((m + 64, 1), 7.0, device=cuda_device)       # the kernel must not write past row m
+    sdf, _, hidden = packed.forward(xp, with_sdf=True, with_feat=False, with_hidden=True)
+    assert (sdf.cpu().double() - ref_sdf).abs().max().item() <= 2e-6 * max(ref_sdf.abs().max().item(), 1.0)
+    buf = torch.zeros(m, k0 + 1, device=cuda_device)
+    buf[:, 1:] = xp
+    sdf_s, _, hidden_s = packed.forward(buf[:, 1:], with_sdf=True, with_feat=False, with_hidden=True)
+    assert torch.equal(hidden, hidden_s)
+    assert (sdf - sdf_s).abs().max().item() <= 1e-6 * max(ref_sdf.abs().max().item(), 1.0)  # head sum order differs
+    assert torch.all(guard == 7.0)
+    # a second launch on the same stream reproduces the first bit for bit
+    sdf2, _ = packed.forward(xp, with_sdf=True, with_feat=False)
+    assert torch.equal(sdf2, sdf)
+
+
 def test_finite_difference_gradient_quality(na_lib, cuda_device):
     """The reason for the split-precision scheme: central differences at eps = 1/2048 through the fused MLP
     must reproduce the float64 directional derivative (a TF32 single pass is off by O(1) here)."""
