@@ -253,6 +253,17 @@ int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, int n, int n_
                    float* feat_out,
                    int64_t ld_feat, float* hidden_out, int64_t ld_hidden, void* stream);
 
+/* SDF-only form of na_sdf_mlp_fwd (h0 and the SDF head; no feature layer) reading its input as CHUNK PLANES:
+ * column 8 c + e of row r is planes[c * chunk_stride + r * 8 + e] -- for 8 features per level exactly the level-major
+ * planes na_hashgrid_taps_fwd_strided writes (chunk = level), followed by one chunk that holds the row's xyz.  The
+ * weights are packed for THAT column order.  k0 = 32 j + r (j in 1..4, r <= 4 columns in the last chunk); n = 128 or
+ * 256.  One launch of the pipelined kernel: W_hi / W_lo resident in shared memory, two accumulator units in TMEM.
+ * Replaces: the same reference code as na_sdf_mlp_fwd with with_feat=False (NeuralSDF.sdf, modules.py:72-74). */
+int na_sdf_head_fwd_planes(const float* planes, int64_t chunk_stride, int64_t m, int k0, int n, const void* w0_hi,
+                           const void* w0_lo, const float* b0, int k0_pad, const float* w_head,
+                           const float* b_head /* device scalar */, float beta, float* sdf_out, float* hidden_out,
+                           int64_t ld_hidden, void* stream);
+
 /* Backward of na_sdf_mlp_fwd with respect to the input rows, plus the pre-activation gradients from which
  * the caller forms the weight gradients (dW1 = dz1^T h0, dW0 = dz0^T x, db = column sums):
  *   dz1 = d_feat * s'(z1);  dh0 = dz1 W1 + d_sdf w_head;  dz0 = dh0 * s'(z0);  dx = dz0 W0.

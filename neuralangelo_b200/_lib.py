@@ -93,6 +93,8 @@ def _declare(lib):
         "na_scale_inplace": (ctypes.c_int, [vp, i64, f32, vp]),
         "na_sdf_mlp_fwd": (ctypes.c_int, [vp, i64, i64, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, vp, ctypes.c_int,
                                           vp, vp, vp, vp, vp, f32, vp, vp, i64, vp, i64, vp]),
+        "na_sdf_head_fwd_planes": (ctypes.c_int, [vp, i64, i64, ctypes.c_int, ctypes.c_int, vp, vp, vp, ctypes.c_int, vp, vp,
+                                                  f32, vp, vp, i64, vp]),
         "na_sdf_mlp_bwd": (ctypes.c_int, [i64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, vp, vp, i64, vp,
                                           vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, i64, vp]),
         "na_mlp_chain_fwd": (ctypes.c_int, [ctypes.POINTER(MlpStage), ctypes.c_int, i64, vp]),

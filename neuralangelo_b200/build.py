@@ -22,7 +22,7 @@ NVCC_FLAGS = [
     "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC,-O3,-Wall",
     "-Xptxas", "-v",
-]
+] + os.environ.get("NA_NVCC_EXTRA", "").split()   # developer builds only (e.g. -DNA_MLP_PROF)
 
 
 def sources():

@@ -67,6 +67,9 @@ struct MlpParams {
     int64_t ld_feat;
     float* hidden_out;    // [M, N] layer-0 activations (for the backward), stride ld_hidden, or null
     int64_t ld_hidden;
+    // chunk-plane input (pipelined kernel only): column 8 c + e of row r is planes[c * chunk_stride + r * 8 + e]
+    const float* planes;
+    int64_t chunk_stride;
 };
 
 // ---------------------------------------------------------------- the kernel
@@ -322,59 +325,72 @@ __global__ void __launch_bounds__(kFwdThreads, 1) sdf_mlp_fwd_kernel(const __gri
 // ==================================================================================================
 // Pipelined form of the forward for the SDF-only evaluation (n_layers == 1: finite-difference taps, the no-grad
 // evaluations of the hierarchical sampler, the lattice queries of the mesh extractor -- four fifths of all point
-// evaluations).  The kernel above runs input staging, MMA and epilogue of a tile one after the other; here they
-// overlap:
-//   * input loader (warp 18): ONE bulk copy (cp.async.bulk) per tile brings the raw fp32 rows -- contiguous in HBM
-//     when the rows are packed -- into a staging buffer while the previous tile is being processed;
-//   * compute warps 0-15: convert the staged rows shared->shared into the split-fp16 A image, then run the
-//     epilogues;
+// evaluations).  The kernel above runs input staging, MMA and epilogue of a tile one after the other and re-streams
+// the weights for every tile; here
+//   * W_hi / W_lo of the single layer stay RESIDENT in shared memory (144 x 256 x 2 x 2 B = 144 KB, loaded once per CTA
+//     by two bulk copies), so the steady state has no weight traffic at all;
 //   * the N columns are processed as two halves ("units"), each with its own D_main / D_cross accumulator pair
 //     (2 x 256 TMEM columns), so the MMAs of one unit run under the epilogue of the other;
-//   * weight loader (warp 17): streams the matching N-half of W_hi / W_lo through a 4-stage ring of 32-wide K blocks.
+//   * the compute warps request the NEXT tile's rows from HBM into registers before they start the first epilogue of
+//     the current tile and convert them into the split-fp16 A image between the two epilogues, when the MMAs that
+//     read the current image have completed (a_free).
 // Barriers (one completion per tile each, parity = local tile index & 1):
-//   raw_full / raw_empty   staging buffer:   input loader <-> compute warps
-//   a_ready / a_free       A image:          compute warps <-> MMA warp (a_free = tcgen05.commit after the 2nd unit)
-//   d_full[h] / d_empty[h] accumulators:     MMA warp <-> compute warps
-// Requirements checked by the host entry point: packed rows (ldx == k0) starting 16-byte aligned, odd k0 (conflict-
-// free column walks of the staging buffer; 3 + levels * features is always odd), hidden width 128 or 256.
+//   a_ready / a_free       A image:      compute warps <-> MMA warp (a_free = tcgen05.commit after the 2nd unit)
+//   d_full[h] / d_empty[h] accumulators: MMA warp <-> compute warps
+// Lane mapping of the input staging: a warp owns 8 rows; lane = (row & 7) + 8 * (k-chunk & 3), so a load instruction
+// covers 8 rows x 128 contiguous bytes and the 16-byte stores of each quarter warp fall into 8 different bank groups.
+// Envelope (host entry point): hidden width 128 or 256, k0 = 32 j + r with r <= 4 (3 + levels * features for every
+// even level * feature product that is a multiple of 32), shared memory fits.
 // ==================================================================================================
+#ifdef NA_MLP_PROF   // developer build (scripts/profile_mlp_phases.py): per-phase clock64 totals of CTA 0
+__device__ unsigned long long na_mlp_prof[16];
+#define PROF_DECL(cond) const bool prof_on = (cond); long long prof_t = clock64()
+#define PROF(i)                                      \
+    do {                                             \
+        if (prof_on) {                               \
+            const long long t1 = clock64();          \
+            na_mlp_prof[i] += (unsigned long long)(t1 - prof_t); \
+            prof_t = t1;                             \
+        }                                            \
+    } while (0)
+#else
+#define PROF_DECL(cond)
+#define PROF(i)
+#endif
+
 constexpr int kPipeWarps = 16;
 constexpr int kPipeCompute = kPipeWarps * 32;
-constexpr int kPipeThreads = kPipeCompute + 96;   // + MMA warp, weight loader, input loader
-constexpr int kPipeStages = 4;
-constexpr int kPipeBlockK = 32;                   // K elements per ring stage (two UMMA k-steps)
-constexpr int kPipeBars = 2 * kPipeStages + 8;
+constexpr int kPipeThreads = kPipeCompute + 32;   // + MMA warp (also loads the weights once)
+constexpr int kPipeBars = 8;
+constexpr int kPipeRounds = 8;                    // up to 8 x 32 input columns
+constexpr int kPipeTail = 4;                      // + up to 4 more
 
-__host__ __device__ inline uint32_t pipe_raw_bytes(int k0) { return ((uint32_t)kTileM * k0 * 4 + 127u) & ~127u; }
-__host__ __device__ inline uint32_t pipe_stage_bytes(int n) { return 2u * (kPipeBlockK / 8) * (uint32_t)(n / 2) * 16u; }
-__host__ __device__ inline uint32_t pipe_smem_bytes(int k0, int k_pad, int n) {
-    return 2u * kTileM * k_pad * 2u + pipe_raw_bytes(k0) + kPipeStages * pipe_stage_bytes(n) +
-           (2u * 4u * kTileM + 2u * kMaxN) * 4u + kPipeBars * 8u + 16u;
+__host__ __device__ inline uint32_t pipe_smem_bytes(int k_pad, int n) {
+    return 2u * kTileM * k_pad * 2u + 2u * (uint32_t)k_pad * n * 2u + (2u * 4u * kTileM + 2u * kMaxN) * 4u +
+           kPipeBars * 8u + 16u;
 }
 
+template <int ROUNDS, bool PLANES>
 __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(const __grid_constant__ MlpParams P) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const int n = P.n, nh = n / 2, k0 = P.k0, k_pad = P.layer[0].k_pad;
     const int chunks = k_pad / 8;
     const uint32_t a_bytes = (uint32_t)kTileM * k_pad * 2;
-    const uint32_t chunk_bytes = (uint32_t)nh * 16;                     // one 8-wide k-chunk of one N half
-    const uint32_t stage_half = (kPipeBlockK / 8) * chunk_bytes;        // the W_hi (or W_lo) part of a ring stage
+    const uint32_t w_bytes = (uint32_t)k_pad * n * 2;
+    const uint32_t chunk_bytes = (uint32_t)n * 16;   // one 8-wide k-chunk of all N columns in the packed weights
     uint8_t* a_hi = smem;
     uint8_t* a_lo = a_hi + a_bytes;
-    uint8_t* raw = a_lo + a_bytes;
-    uint8_t* b_ring = raw + pipe_raw_bytes(k0);
-    float* head_partial = reinterpret_cast<float*>(b_ring + kPipeStages * 2 * stage_half);   // [2][4][kTileM]
+    uint8_t* w_hi = a_lo + a_bytes;
+    uint8_t* w_lo = w_hi + w_bytes;
+    float* head_partial = reinterpret_cast<float*>(w_lo + w_bytes);   // [2][4][kTileM]
     float* s_bias = head_partial + 2 * 4 * kTileM;
     float* s_head = s_bias + kMaxN;
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_head + kMaxN);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kPipeBars);
     const uint32_t bar0 = smem_u32(bars);
-    auto b_full = [&](int s) { return bar0 + 8u * s; };
-    auto b_empty = [&](int s) { return bar0 + 8u * (kPipeStages + s); };
-    const uint32_t raw_full = bar0 + 8u * (2 * kPipeStages), raw_empty = raw_full + 8u, a_ready = raw_full + 16u,
-                   a_free = raw_full + 24u;
-    auto d_full = [&](int h) { return raw_full + 32u + 8u * h; };
-    auto d_empty = [&](int h) { return raw_full + 48u + 8u * h; };
+    const uint32_t w_full = bar0, a_ready = bar0 + 8u, a_free = bar0 + 16u;
+    auto d_full = [&](int h) { return bar0 + 24u + 8u * h; };
+    auto d_empty = [&](int h) { return bar0 + 40u + 8u * h; };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t n_tiles = (P.m + kTileM - 1) / kTileM;
@@ -385,12 +401,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
         s_head[i] = head ? P.w_head[i] : 0.f;
     }
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kPipeStages; ++s) {
-            mbar_init(b_full(s), 1);
-            mbar_init(b_empty(s), 1);
-        }
-        mbar_init(raw_full, 1);
-        mbar_init(raw_empty, kPipeCompute);
+        mbar_init(w_full, 1);
         mbar_init(a_ready, kPipeCompute);
         mbar_init(a_free, 1);
         for (int h = 0; h < 2; ++h) {
@@ -410,125 +421,112 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;   // unit h: D_main at columns [256 h, 256 h + nh), D_cross at + 128
 
-    if (warp == kPipeWarps + 2) {
-        // ===================== input loader =====================
+    if (warp == kPipeWarps) {
+        // ===================== weights (once) + MMA issuer =====================
         if (lane == 0) {
-            auto issue = [&](int64_t tile) {
-                const int64_t row0 = tile * kTileM;
-                const int rows = (int)(P.m - row0 < kTileM ? P.m - row0 : kTileM);
-                const float* src = P.x + row0 * k0;
-                const uint32_t bytes = (uint32_t)rows * k0 * 4, bulk = bytes & ~15u;
-                float* rawf = reinterpret_cast<float*>(raw);
-                for (uint32_t w = bulk / 4; w < bytes / 4; ++w) rawf[w] = __ldg(src + w);   // < 16-byte tail of the last tile
-                mbar_expect_tx(raw_full, bulk);
-                bulk_copy_g2s(smem_u32(raw), src, bulk, raw_full);
-            };
-            if ((int64_t)blockIdx.x < n_tiles) issue(blockIdx.x);
-            uint32_t q = 0;
-            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
-                mbar_wait(raw_empty, q & 1);
-                if (tile + gridDim.x < n_tiles) issue(tile + gridDim.x);
-            }
-        }
-    } else if (warp == kPipeWarps + 1) {
-        // ===================== weight loader =====================
-        if (lane == 0) {
-            const uint8_t* w_hi = reinterpret_cast<const uint8_t*>(P.layer[0].w_hi);
-            const uint8_t* w_lo = reinterpret_cast<const uint8_t*>(P.layer[0].w_lo);
-            uint32_t it = 0;
-            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                for (int h = 0; h < 2; ++h) {
-                    for (int c0 = 0; c0 < chunks; c0 += kPipeBlockK / 8, ++it) {
-                        const int s = it % kPipeStages;
-                        mbar_wait(b_empty(s), ((it / kPipeStages) & 1) ^ 1);
-                        const int nc = min(kPipeBlockK / 8, chunks - c0);
-                        mbar_expect_tx(b_full(s), 2u * nc * chunk_bytes);
-                        const uint32_t dst = smem_u32(b_ring + s * 2 * stage_half);
-                        for (int c = 0; c < nc; ++c) {
-                            const size_t src = (size_t)(c0 + c) * ((size_t)n * 16) + (size_t)h * chunk_bytes;
-                            bulk_copy_g2s(dst + c * chunk_bytes, w_hi + src, chunk_bytes, b_full(s));
-                            bulk_copy_g2s(dst + stage_half + c * chunk_bytes, w_lo + src, chunk_bytes, b_full(s));
-                        }
-                    }
-                }
-            }
-        }
-    } else if (warp == kPipeWarps) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
+            mbar_expect_tx(w_full, 2u * w_bytes);
+            bulk_copy_g2s(smem_u32(w_hi), P.layer[0].w_hi, w_bytes, w_full);
+            bulk_copy_g2s(smem_u32(w_lo), P.layer[0].w_lo, w_bytes, w_full);
+            mbar_wait(w_full, 0);
             const uint32_t idesc = make_idesc(kTileM, nh);
             const uint32_t a_lbo = kTileM / 8 * 128;
-            uint32_t it = 0, q = 0;
+            uint32_t q = 0;
+            PROF_DECL(blockIdx.x == 0);
             for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
                 mbar_wait(a_ready, q & 1);
                 tc_fence_after();
+                PROF(8);
                 for (int h = 0; h < 2; ++h) {
                     if (q > 0) {   // the epilogue of the previous tile has drained this accumulator pair
                         mbar_wait(d_empty(h), (q - 1) & 1);
                         tc_fence_after();
                     }
+                    PROF(9 + 2 * h);
                     const uint32_t d_main = tmem_base + 256u * h, d_cross = d_main + 128u;
-                    bool first = true;
-                    for (int c0 = 0; c0 < chunks; c0 += kPipeBlockK / 8, ++it) {
-                        const int s = it % kPipeStages;
-                        mbar_wait(b_full(s), (it / kPipeStages) & 1);
-                        tc_fence_after();
-                        const int nc = min(kPipeBlockK / 8, chunks - c0);
-                        const uint32_t b_hi_addr = smem_u32(b_ring + s * 2 * stage_half);
-                        const uint32_t b_lo_addr = b_hi_addr + stage_half;
-                        for (int c = 0; c < nc; c += 2) {
-                            const uint32_t a_off = (uint32_t)(c0 + c) * a_lbo, b_off = (uint32_t)c * chunk_bytes;
-                            const uint64_t ah = make_desc(smem_u32(a_hi) + a_off, a_lbo, 128);
-                            const uint64_t al = make_desc(smem_u32(a_lo) + a_off, a_lbo, 128);
-                            const uint64_t bh = make_desc(b_hi_addr + b_off, chunk_bytes, 128);
-                            const uint64_t bl = make_desc(b_lo_addr + b_off, chunk_bytes, 128);
-                            tc_mma_f16(d_cross, al, bh, idesc, first ? 0u : 1u);
-                            tc_mma_f16(d_cross, ah, bl, idesc, 1u);
-                            tc_mma_f16(d_main, ah, bh, idesc, first ? 0u : 1u);
-                            first = false;
-                        }
-                        tc_commit(b_empty(s));
+                    const uint32_t b_half = (uint32_t)h * nh * 16;   // N half inside a k-chunk of the packed weights
+                    for (int c = 0; c < chunks; c += 2) {            // one UMMA k-step = 16 elements = 2 chunks
+                        const uint32_t a_off = (uint32_t)c * a_lbo, b_off = (uint32_t)c * chunk_bytes + b_half;
+                        const uint64_t ah = make_desc(smem_u32(a_hi) + a_off, a_lbo, 128);
+                        const uint64_t al = make_desc(smem_u32(a_lo) + a_off, a_lbo, 128);
+                        const uint64_t bh = make_desc(smem_u32(w_hi) + b_off, chunk_bytes, 128);
+                        const uint64_t bl = make_desc(smem_u32(w_lo) + b_off, chunk_bytes, 128);
+                        tc_mma_f16(d_cross, al, bh, idesc, c ? 1u : 0u);
+                        tc_mma_f16(d_cross, ah, bl, idesc, 1u);
+                        tc_mma_f16(d_main, ah, bh, idesc, c ? 1u : 0u);
                     }
                     tc_commit(d_full(h));
+                    PROF(10 + 2 * h);
                 }
                 tc_commit(a_free);   // every MMA that reads this tile's A image has completed
             }
         }
     } else {
         // ===================== compute warps =====================
-        const int tid = threadIdx.x;
         const int quarter = warp & 3, group = warp >> 2;
         const int cpg = nh / 4 >= 16 ? nh / 4 : 16;       // columns of a unit per warp group
         const int n_groups = nh / cpg;
-        const int row = quarter * 32 + lane;
+        const int row = quarter * 32 + lane;              // accumulator row == TMEM lane
         const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
         const float inv_beta = 1.f / P.beta;
-        const float* rawf = reinterpret_cast<const float*>(raw);
+        // input staging: this thread converts row s_row, k-chunks 4 u + s_kc (u < ROUNDS) and, in lanes 0-7, the
+        // remainder columns [32 ROUNDS, k0)
+        const int s_row = warp * 8 + (lane & 7), s_kc = lane >> 3;
+        const int tail_cols = k0 - 32 * ROUNDS;           // 0..kPipeTail
+        float pre[ROUNDS][8], tailv[kPipeTail];
 
-        // staged fp32 rows -> split-fp16 A image; consecutive lanes take consecutive rows: the column walk of the
-        // staging buffer has an odd word stride (k0) and the 16-byte stores are consecutive -- both conflict-free
-        auto convert = [&](int rows) {
-            const int total = kTileM * chunks;
-            for (int idx = tid; idx < total; idx += kPipeCompute) {
-                const int r = idx & (kTileM - 1), kc = idx / kTileM;
-                const float* src = rawf + r * k0 + kc * 8;
-                uint32_t hi[4], lo[4];
+        auto prefetch = [&](int64_t tile) {
+            const int64_t gr = tile * kTileM + s_row;
+            const bool ok = gr < P.m;
+            if (PLANES) {   // [chunk][row][8] fp32: two aligned 16-byte loads per chunk, 256 contiguous bytes per 8 lanes
+                const float* src = P.planes + gr * 8;
+                const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int col = kc * 8 + 2 * j;
-                    const float v0 = (r < rows && col < k0) ? src[2 * j] : 0.f;
-                    const float v1 = (r < rows && col + 1 < k0) ? src[2 * j + 1] : 0.f;
-                    __half h0, l0, h1, l1;
-                    split_f16(v0, h0, l0);
-                    split_f16(v1, h1, l1);
-                    hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                for (int u = 0; u < ROUNDS; ++u) {
+                    const float4* c = reinterpret_cast<const float4*>(src + (int64_t)(4 * u + s_kc) * P.chunk_stride);
+                    const float4 lo4 = ok ? __ldg(c) : z, hi4 = ok ? __ldg(c + 1) : z;
+                    pre[u][0] = lo4.x, pre[u][1] = lo4.y, pre[u][2] = lo4.z, pre[u][3] = lo4.w;
+                    pre[u][4] = hi4.x, pre[u][5] = hi4.y, pre[u][6] = hi4.z, pre[u][7] = hi4.w;
                 }
-                const uint32_t off = a_chunk_offset(r, kc);
-                *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                const float4 t4 = (ok && s_kc == 0 && tail_cols > 0)
+                                      ? __ldg(reinterpret_cast<const float4*>(src + (int64_t)(4 * ROUNDS) * P.chunk_stride))
+                                      : z;
+                tailv[0] = t4.x, tailv[1] = t4.y, tailv[2] = t4.z, tailv[3] = t4.w;
+#pragma unroll
+                for (int e = 0; e < kPipeTail; ++e) tailv[e] = e < tail_cols ? tailv[e] : 0.f;
+            } else {
+                const float* src = P.x + gr * P.ldx;
+#pragma unroll
+                for (int u = 0; u < ROUNDS; ++u)
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) pre[u][e] = ok ? __ldg(src + (4 * u + s_kc) * 8 + e) : 0.f;
+#pragma unroll
+                for (int e = 0; e < kPipeTail; ++e)
+                    tailv[e] = (ok && s_kc == 0 && e < tail_cols) ? __ldg(src + 32 * ROUNDS + e) : 0.f;
             }
         };
-        auto rows_of = [&](int64_t tile) { return (int)(P.m - tile * kTileM < kTileM ? P.m - tile * kTileM : kTileM); };
+        auto store_chunk = [&](int kc, const float* v) {
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                __half h0, l0, h1, l1;
+                split_f16(v[2 * j], h0, l0);
+                split_f16(v[2 * j + 1], h1, l1);
+                hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+            }
+            const uint32_t off = a_chunk_offset(s_row, kc);
+            *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        };
+        auto convert = [&]() {
+#pragma unroll
+            for (int u = 0; u < ROUNDS; ++u) store_chunk(4 * u + s_kc, pre[u]);
+            if (s_kc == 0 && tail_cols > 0) {
+                float v[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = e < kPipeTail ? tailv[e] : 0.f;
+                store_chunk(4 * ROUNDS, v);
+            }
+        };
 
         float dot = 0.f;
         auto epilogue = [&](int h, int64_t row0) {
@@ -543,10 +541,16 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
                 const int gc = h * nh + c0;   // column of the layer
                 float act[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const float pre = fmaf(__uint_as_float(rc[j]), kLoInv, __uint_as_float(rm[j])) + s_bias[gc + j];
-                    act[j] = softplus(pre, P.beta, inv_beta);
-                    dot = fmaf(act[j], s_head[gc + j], dot);
+                for (int j = 0; j < 16; j += 4) {
+                    const float4 b4 = *reinterpret_cast<const float4*>(s_bias + gc + j);
+                    const float4 h4 = *reinterpret_cast<const float4*>(s_head + gc + j);
+                    const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float p = fmaf(__uint_as_float(rc[j + e]), kLoInv, __uint_as_float(rm[j + e])) + bb[e];
+                        act[j + e] = softplus(p, P.beta, inv_beta);
+                        dot = fmaf(act[j + e], hh[e], dot);
+                    }
                 }
                 if (P.hidden_out && row0 + row < P.m) {
                     float* dst = P.hidden_out + (row0 + row) * P.ld_hidden + gc;
@@ -557,36 +561,48 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
             }
         };
 
+        // the zero padding of the A image (k-chunks past the last input column) is written once
+        for (int kc = 4 * ROUNDS + (tail_cols > 0 ? 1 : 0) + s_kc; kc < chunks; kc += 4) {
+            const uint32_t off = a_chunk_offset(s_row, kc);
+            *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(0u, 0u, 0u, 0u);
+            *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(0u, 0u, 0u, 0u);
+        }
         uint32_t q = 0;
         if ((int64_t)blockIdx.x < n_tiles) {   // prologue: the first tile's A image
-            mbar_wait(raw_full, 0);
-            convert(rows_of(blockIdx.x));
-            mbar_arrive(raw_empty);
+            prefetch(blockIdx.x);
+            convert();
             fence_proxy_async();
             mbar_arrive(a_ready);
         }
+        PROF_DECL(blockIdx.x == 0 && threadIdx.x == 0);
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
             const int64_t row0 = tile * kTileM;
             const int64_t next = tile + gridDim.x;
+            if (next < n_tiles) prefetch(next);   // in flight during the first epilogue
             dot = 0.f;
+            PROF(0);
             mbar_wait(d_full(0), q & 1);
             tc_fence_after();
+            PROF(1);
             epilogue(0, row0);
             tc_fence_before();
             mbar_arrive(d_empty(0));
-            if (next < n_tiles) {   // next tile's A image, while the second unit's MMAs / the next first unit's run
+            PROF(2);
+            if (next < n_tiles) {   // next tile's A image, under the second unit's MMAs
                 mbar_wait(a_free, q & 1);
-                mbar_wait(raw_full, (q + 1) & 1);
-                convert(rows_of(next));
-                mbar_arrive(raw_empty);
+                PROF(3);
+                convert();
                 fence_proxy_async();
                 mbar_arrive(a_ready);
+                PROF(4);
             }
             mbar_wait(d_full(1), q & 1);
             tc_fence_after();
+            PROF(5);
             epilogue(1, row0);
             tc_fence_before();
             mbar_arrive(d_empty(1));
+            PROF(6);
             if (head && P.sdf_out) {
                 float* part = head_partial + (q & 1) * 4 * kTileM;
                 part[group * kTileM + row] = dot;   // groups without columns contribute 0
@@ -595,6 +611,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
                     P.sdf_out[row0 + row] = __ldg(P.b_head) + part[row] + part[kTileM + row] + part[2 * kTileM + row] +
                                             part[3 * kTileM + row];
             }
+            PROF(7);
         }
     }
 
@@ -603,6 +620,18 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
     if (warp == kPipeWarps) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+using PipeKernel = void (*)(const MlpParams);
+template <bool PLANES>
+PipeKernel pipe_kernel_for(int rounds) {
+    switch (rounds) {
+        case 1: return sdf_head_fwd_pipe_kernel<1, PLANES>;
+        case 2: return sdf_head_fwd_pipe_kernel<2, PLANES>;
+        case 3: return sdf_head_fwd_pipe_kernel<3, PLANES>;
+        case 4: return sdf_head_fwd_pipe_kernel<4, PLANES>;
+        default: return nullptr;
     }
 }
 
@@ -907,7 +936,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_c
 // The opt-in to > 48 KB of dynamic shared memory is per device and is not a stream operation: do it once per
 // (kernel, device) so that later launches -- possibly under CUDA-graph capture -- make no attribute call.
 int ensure_smem_attr(int which, const void* func, const char* what, int smem_bytes) {
-    static bool done[3][64] = {};
+    static bool done[10][64] = {};
     int dev = 0;
     if (int rc = na::check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return rc;
     if (dev < 0 || dev >= 64 || !done[which][dev]) {
@@ -920,6 +949,17 @@ int ensure_smem_attr(int which, const void* func, const char* what, int smem_byt
 }
 
 }  // namespace
+
+#ifdef NA_MLP_PROF
+extern "C" int na_dev_mlp_prof(unsigned long long* out16, int reset) {
+    if (out16 && cudaMemcpyFromSymbol(out16, na_mlp_prof, sizeof(unsigned long long) * 16) != cudaSuccess) return -1;
+    if (reset) {
+        unsigned long long z[16] = {};
+        if (cudaMemcpyToSymbol(na_mlp_prof, z, sizeof(z)) != cudaSuccess) return -1;
+    }
+    return 0;
+}
+#endif
 
 extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, int n, int n_layers,
                               const void* w0_hi, const void* w0_lo, const float* b0, int k0_pad, const void* w1_hi,
@@ -950,21 +990,60 @@ extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, in
     P.sdf_out = sdf_out, P.feat_out = feat_out, P.ld_feat = ld_feat, P.hidden_out = hidden_out, P.ld_hidden = ld_hidden;
     const int64_t tiles = (m + kTileM - 1) / kTileM;
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
-    // SDF-only evaluation of packed rows: the pipelined kernel (NA_MLP_NO_PIPE=1 is a developer switch for A/B runs)
+    // SDF-only evaluation: the pipelined kernel with resident weights (NA_MLP_NO_PIPE=1: developer switch for A/B runs)
     static const bool no_pipe = getenv("NA_MLP_NO_PIPE") != nullptr;
-    const uint32_t pipe_smem = pipe_smem_bytes(k0, k0_pad, n);
-    if (!no_pipe && n_layers == 1 && ldx == k0 && (k0 & 1) && n % 128 == 0 && (uintptr_t)x % 16 == 0 &&
+    const uint32_t pipe_smem = pipe_smem_bytes(k0_pad, n);
+    const int rounds = k0 / 32;
+    if (!no_pipe && n_layers == 1 && n % 128 == 0 && k0 - 32 * rounds <= kPipeTail && pipe_kernel_for<false>(rounds) &&
         pipe_smem <= 227u * 1024u) {
-        if (int rc = ensure_smem_attr(2, (const void*)sdf_head_fwd_pipe_kernel,
-                                      "cudaFuncSetAttribute(sdf_head_fwd_pipe_kernel)", 227 * 1024))
+        const PipeKernel kern = pipe_kernel_for<false>(rounds);
+        if (int rc = ensure_smem_attr(1 + rounds, (const void*)kern, "cudaFuncSetAttribute(sdf_head_fwd_pipe_kernel)",
+                                      227 * 1024))
             return rc;
-        sdf_head_fwd_pipe_kernel<<<grid, kPipeThreads, pipe_smem, (cudaStream_t)stream>>>(P);
+        kern<<<grid, kPipeThreads, pipe_smem, (cudaStream_t)stream>>>(P);
         NA_CHECK_LAUNCH("sdf_head_fwd_pipe_kernel");
         return NA_OK;
     }
     if (int rc = ensure_smem_attr(0, (const void*)sdf_mlp_fwd_kernel, "cudaFuncSetAttribute(sdf_mlp_fwd_kernel)", kFwdSmemBytes)) return rc;
     sdf_mlp_fwd_kernel<<<grid, kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(P);
     NA_CHECK_LAUNCH("sdf_mlp_fwd_kernel");
+    return NA_OK;
+}
+
+extern "C" int na_sdf_head_fwd_planes(const float* planes, int64_t chunk_stride, int64_t m, int k0, int n,
+                                      const void* w0_hi, const void* w0_lo, const float* b0, int k0_pad,
+                                      const float* w_head, const float* b_head, float beta, float* sdf_out,
+                                      float* hidden_out, int64_t ld_hidden, void* stream) {
+    na::clear_error();
+    NA_REQUIRE(m >= 0, "sdf_head_fwd_planes: negative row count");
+    if (m == 0) return NA_OK;
+    NA_REQUIRE(planes && w0_hi && w0_lo && b0, "sdf_head_fwd_planes: null pointer");
+    NA_REQUIRE(!w_head || b_head, "sdf_head_fwd_planes: w_head given without b_head");
+    NA_REQUIRE((uintptr_t)planes % 16 == 0 && chunk_stride % 4 == 0 && chunk_stride >= m * 8,
+               "sdf_head_fwd_planes: planes must be 16-byte aligned with chunk_stride a multiple of 4 and >= 8 m");
+    const int rounds = k0 / 32;
+    NA_REQUIRE(n % 128 == 0 && n >= 128 && n <= kMaxN, "sdf_head_fwd_planes: hidden width %d unsupported (128, 256)", n);
+    NA_REQUIRE(k0 >= 32 && k0 - 32 * rounds <= kPipeTail && pipe_kernel_for<true>(rounds) != nullptr,
+               "sdf_head_fwd_planes: k0=%d unsupported (32 j + r, j in 1..4, r <= %d)", k0, kPipeTail);
+    NA_REQUIRE(k0 <= k0_pad && k0_pad % 16 == 0 && k0_pad <= kMaxK, "sdf_head_fwd_planes: k0_pad=%d unsupported", k0_pad);
+    NA_REQUIRE(beta > 0.f, "sdf_head_fwd_planes: softplus beta must be positive");
+    NA_REQUIRE(!hidden_out || (ld_hidden % 4 == 0 && (uintptr_t)hidden_out % 16 == 0),
+               "sdf_head_fwd_planes: hidden_out needs 16-byte alignment and a stride multiple of 4");
+    NA_REQUIRE(((uintptr_t)w0_hi | (uintptr_t)w0_lo) % 16 == 0, "sdf_head_fwd_planes: packed weights must be 16-byte aligned");
+    const uint32_t smem = pipe_smem_bytes(k0_pad, n);
+    NA_REQUIRE(smem <= 227u * 1024u, "sdf_head_fwd_planes: k0_pad=%d x n=%d weights do not fit in shared memory", k0_pad, n);
+    MlpParams P{};
+    P.planes = planes, P.chunk_stride = chunk_stride, P.m = m, P.k0 = k0, P.n = n, P.n_layers = 1;
+    P.layer[0] = Layer{(const __half*)w0_hi, (const __half*)w0_lo, b0, k0_pad};
+    P.w_head = w_head, P.b_head = b_head, P.beta = beta;
+    P.sdf_out = sdf_out, P.hidden_out = hidden_out, P.ld_hidden = ld_hidden;
+    const PipeKernel kern = pipe_kernel_for<true>(rounds);
+    if (int rc = ensure_smem_attr(5 + rounds, (const void*)kern, "cudaFuncSetAttribute(sdf_head_fwd_pipe_kernel)", 227 * 1024))
+        return rc;
+    const int64_t tiles = (m + kTileM - 1) / kTileM;
+    const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
+    kern<<<grid, kPipeThreads, smem, (cudaStream_t)stream>>>(P);
+    NA_CHECK_LAUNCH("sdf_head_fwd_pipe_kernel");
     return NA_OK;
 }
 

@@ -57,6 +57,9 @@ class PackedSdfMlp:
         with torch.no_grad():
             new = dict(zip(("w0_hi", "w0_lo"), pack_weight(l0.effective_weight(), self.k0_pad)))
             new.update(zip(("w1_hi", "w1_lo"), pack_weight(l1.effective_weight(), self.n)))
+            # chunk-plane column order: encoding features first (one 8-wide chunk per level), xyz in the last chunk
+            w0 = l0.effective_weight()
+            new.update(zip(("w0p_hi", "w0p_lo"), pack_weight(torch.cat([w0[:, 3:], w0[:, :3]], dim=1), self.k0_pad)))
             new["b0"] = l0.bias.detach().float().contiguous()
             new["b1"] = l1.bias.detach().float().contiguous()
             new["w_head"] = mlp.linear_sdf.weight.detach().float().reshape(-1).contiguous()
@@ -85,6 +88,23 @@ class PackedSdfMlp:
                                  ptr(sdf), ptr(feat), self.n, ptr(hidden), self.n, _lib.current_stream())
         _lib.check(rc, "na_sdf_mlp_fwd")
         return (sdf, feat, hidden) if with_hidden else (sdf, feat)
+
+
+    def forward_planes(self, planes, m, with_hidden=False):
+        """SDF-only evaluation of chunk planes: planes [C, M_alloc, 8] fp32 (C = ceil(k0 / 8) chunks; chunk c < C-1 is
+        encoding level c, the last chunk holds xyz in its first three floats), rows [0, m).  Returns sdf [m,1]
+        (and the hidden activations [m,n])."""
+        _lib.require_cuda(planes)
+        assert planes.dim() == 3 and planes.shape[2] == 8 and planes.stride(2) == 1 and planes.stride(1) == 8
+        assert planes.shape[0] * 8 >= self.k0 and planes.shape[1] >= m and planes.dtype == torch.float32
+        dev = planes.device
+        sdf = torch.empty(m, 1, dtype=torch.float32, device=dev)
+        hidden = torch.empty(m, self.n, dtype=torch.float32, device=dev) if with_hidden else None
+        rc = _L().na_sdf_head_fwd_planes(ptr(planes), planes.stride(0), m, self.k0, self.n, ptr(self.w0p_hi),
+                                         ptr(self.w0p_lo), ptr(self.b0), self.k0_pad, ptr(self.w_head), ptr(self.b_head),
+                                         self.beta, ptr(sdf), ptr(hidden), self.n, _lib.current_stream())
+        _lib.check(rc, "na_sdf_head_fwd_planes")
+        return (sdf, hidden) if with_hidden else sdf
 
 
 class FusedSdfMlpFunction(torch.autograd.Function):

@@ -29,4 +29,6 @@ for name, wf in (("sdf_only", False), ("sdf_feat", True)):
     with torch.no_grad():
         ms_t = timeit(lambda: mlp(x, with_sdf=True, with_feat=wf))
     res[name]["torch_fp32_ms"] = ms_t
+planes = torch.randn(17, m, 8, device=dev)
+res["sdf_only_planes_ms"] = timeit(lambda: packed.forward_planes(planes, m))
 print(json.dumps(res, indent=1))
