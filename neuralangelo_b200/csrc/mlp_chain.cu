@@ -216,10 +216,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_fwd_kernel(const __grid
                                 uint32_t hi[4], lo[4];
 #pragma unroll
                                 for (int j = 0; j < 4; ++j) {
-                                    __half h0, l0, h1, l1;
-                                    split_f16(act[q * 8 + j * 2], h0, l0);
-                                    split_f16(act[q * 8 + j * 2 + 1], h1, l1);
-                                    hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                                    split2_f16(act[q * 8 + j * 2], act[q * 8 + j * 2 + 1], hi[j], lo[j]);
                                 }
                                 const uint32_t off = a_chunk_offset(row, c0 / 8 + q);
                                 *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
@@ -268,10 +265,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_fwd_kernel(const __grid
                             uint32_t hi[4], lo[4];
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
-                                __half h0, l0, h1, l1;
-                                split_f16(v[u][2 * j], h0, l0);
-                                split_f16(v[u][2 * j + 1], h1, l1);
-                                hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                                split2_f16(v[u][2 * j], v[u][2 * j + 1], hi[j], lo[j]);
                             }
                             const uint32_t off = a_chunk_offset(r, kc);
                             *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);

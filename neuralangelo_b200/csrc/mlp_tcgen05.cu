@@ -230,10 +230,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) sdf_mlp_fwd_kernel(const __gri
                         uint32_t hi[4], lo[4];
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            __half h0, l0, h1, l1;
-                            split_f16(v[u][2 * j], h0, l0);
-                            split_f16(v[u][2 * j + 1], h1, l1);
-                            hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                            split2_f16(v[u][2 * j], v[u][2 * j + 1], hi[j], lo[j]);
                         }
                         const uint32_t off = a_chunk_offset(r, kc);
                         *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
@@ -272,10 +269,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) sdf_mlp_fwd_kernel(const __gri
                             uint32_t hi[4], lo[4];
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
-                                __half h0, l0, h1, l1;
-                                split_f16(act[q * 8 + j * 2], h0, l0);
-                                split_f16(act[q * 8 + j * 2 + 1], h1, l1);
-                                hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                                split2_f16(act[q * 8 + j * 2], act[q * 8 + j * 2 + 1], hi[j], lo[j]);
                             }
                             const uint32_t off = a_chunk_offset(row, c0 / 8 + q);
                             *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
@@ -474,44 +468,46 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
         const int tail_cols = k0 - 32 * ROUNDS;           // 0..kPipeTail
         float pre[ROUNDS][8], tailv[kPipeTail];
 
-        auto prefetch = [&](int64_t tile) {
+        // load step `step` of tile `tile` into registers: steps 0..ROUNDS-1 are the rounds of four k-chunks, step
+        // ROUNDS the remainder columns.
+        auto load_step = [&](int64_t tile, int step) {
             const int64_t gr = tile * kTileM + s_row;
-            const bool ok = gr < P.m;
-            if (PLANES) {   // [chunk][row][8] fp32: two aligned 16-byte loads per chunk, 256 contiguous bytes per 8 lanes
-                const float* src = P.planes + gr * 8;
-                const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            const bool ok = tile < n_tiles && gr < P.m;
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-                for (int u = 0; u < ROUNDS; ++u) {
-                    const float4* c = reinterpret_cast<const float4*>(src + (int64_t)(4 * u + s_kc) * P.chunk_stride);
+            for (int u = 0; u < ROUNDS; ++u) {
+                if (u != step) continue;
+                if (PLANES) {   // [chunk][row][8] fp32: two aligned 16-byte loads per chunk, 256 contiguous bytes per 8 lanes
+                    const float4* c = reinterpret_cast<const float4*>(P.planes + gr * 8 + (int64_t)(4 * u + s_kc) * P.chunk_stride);
                     const float4 lo4 = ok ? __ldg(c) : z, hi4 = ok ? __ldg(c + 1) : z;
                     pre[u][0] = lo4.x, pre[u][1] = lo4.y, pre[u][2] = lo4.z, pre[u][3] = lo4.w;
                     pre[u][4] = hi4.x, pre[u][5] = hi4.y, pre[u][6] = hi4.z, pre[u][7] = hi4.w;
+                } else {
+                    const float* src = P.x + gr * P.ldx + (4 * u + s_kc) * 8;
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) pre[u][e] = ok ? __ldg(src + e) : 0.f;
                 }
-                const float4 t4 = (ok && s_kc == 0 && tail_cols > 0)
-                                      ? __ldg(reinterpret_cast<const float4*>(src + (int64_t)(4 * ROUNDS) * P.chunk_stride))
-                                      : z;
-                tailv[0] = t4.x, tailv[1] = t4.y, tailv[2] = t4.z, tailv[3] = t4.w;
+            }
+            if (step == ROUNDS) {
+                if (PLANES) {
+                    const float4 t4 = (ok && s_kc == 0 && tail_cols > 0)
+                                          ? __ldg(reinterpret_cast<const float4*>(P.planes + gr * 8 + (int64_t)(4 * ROUNDS) * P.chunk_stride))
+                                          : z;
+                    tailv[0] = t4.x, tailv[1] = t4.y, tailv[2] = t4.z, tailv[3] = t4.w;
 #pragma unroll
-                for (int e = 0; e < kPipeTail; ++e) tailv[e] = e < tail_cols ? tailv[e] : 0.f;
-            } else {
-                const float* src = P.x + gr * P.ldx;
+                    for (int e = 0; e < kPipeTail; ++e) tailv[e] = e < tail_cols ? tailv[e] : 0.f;
+                } else {
+                    const float* src = P.x + gr * P.ldx + 32 * ROUNDS;
 #pragma unroll
-                for (int u = 0; u < ROUNDS; ++u)
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) pre[u][e] = ok ? __ldg(src + (4 * u + s_kc) * 8 + e) : 0.f;
-#pragma unroll
-                for (int e = 0; e < kPipeTail; ++e)
-                    tailv[e] = (ok && s_kc == 0 && e < tail_cols) ? __ldg(src + 32 * ROUNDS + e) : 0.f;
+                    for (int e = 0; e < kPipeTail; ++e) tailv[e] = (ok && s_kc == 0 && e < tail_cols) ? __ldg(src + e) : 0.f;
+                }
             }
         };
         auto store_chunk = [&](int kc, const float* v) {
             uint32_t hi[4], lo[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                __half h0, l0, h1, l1;
-                split_f16(v[2 * j], h0, l0);
-                split_f16(v[2 * j + 1], h1, l1);
-                hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                split2_f16(v[2 * j], v[2 * j + 1], hi[j], lo[j]);
             }
             const uint32_t off = a_chunk_offset(s_row, kc);
             *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
@@ -569,7 +565,8 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
         }
         uint32_t q = 0;
         if ((int64_t)blockIdx.x < n_tiles) {   // prologue: the first tile's A image
-            prefetch(blockIdx.x);
+#pragma unroll
+            for (int st = 0; st <= ROUNDS; ++st) load_step(blockIdx.x, st);
             convert();
             fence_proxy_async();
             mbar_arrive(a_ready);
@@ -578,7 +575,8 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
             const int64_t row0 = tile * kTileM;
             const int64_t next = tile + gridDim.x;
-            if (next < n_tiles) prefetch(next);   // in flight during the first epilogue
+#pragma unroll
+            for (int st = 0; st <= ROUNDS; ++st) load_step(next, st);   // in flight during the first epilogue
             dot = 0.f;
             PROF(0);
             mbar_wait(d_full(0), q & 1);
@@ -802,10 +800,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_c
                 uint32_t hi[4], lo[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    __half h0, l0, h1, l1;
-                    split_f16(v[q * 8 + j * 2] * scale, h0, l0);
-                    split_f16(v[q * 8 + j * 2 + 1] * scale, h1, l1);
-                    hi[j] = pack2(h0, h1), lo[j] = pack2(l0, l1);
+                    split2_f16(v[q * 8 + j * 2] * scale, v[q * 8 + j * 2 + 1] * scale, hi[j], lo[j]);
                 }
                 const uint32_t off = a_chunk_offset(row, c0 / 8 + q);
                 *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);

@@ -88,21 +88,25 @@ __device__ __forceinline__ uint32_t make_idesc(int m, int n) {
     return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
-__device__ __forceinline__ void split_f16(float v, __half& hi, __half& lo) {
-    v = fminf(fmaxf(v, -65504.f), 65504.f);
-    hi = __float2half_rn(v);
-    lo = __float2half_rn((v - __half2float(hi)) * kLoScale);
-}
-
-__device__ __forceinline__ uint32_t pack2(__half a, __half b) {
-    return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
+// Two values -> packed fp16 pairs (first value in the low half): v = hi + 2^-11 lo'.  One F2FP.SATFINITE.PACK_AB per
+// pair and piece (the scalar cvt.f16.f32 path is a quarter-rate F2F per element and bounded the staging phases);
+// satfinite clamps to +-65504 instead of producing inf.
+__device__ __forceinline__ void split2_f16(float v0, float v1, uint32_t& hi, uint32_t& lo) {
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(v1), "f"(v0));
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"((v1 - f.y) * kLoScale), "f"((v0 - f.x) * kLoScale));
 }
 
 // softplus_beta(x) = max(x,0) + log(1 + exp(-|beta x|)) / beta.  Differs from torch's thresholded form
 // (x when beta*x > 20) by < exp(-20)/beta; the fast exp/log intrinsics are accurate to ~1e-7 ABSOLUTE on the
 // log term, i.e. ~1e-9 on the result for beta = 100 -- far below the fp32 rounding of the sums around it.
 __device__ __forceinline__ float softplus(float x, float beta, float inv_beta) {
-    return fmaxf(x, 0.f) + __logf(1.f + __expf(-fabsf(beta * x))) * inv_beta;
+    // raw ex2 / lg2 (ftz): the range fix-ups of __expf only matter below 2^-126, which vanishes against the 1 it is
+    // added to; the constant products are loop-invariant
+    float e, l;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fabsf(x) * (beta * -1.4426950408889634f)));
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(1.f + e));
+    return fmaf(l, 0.6931471805599453f * inv_beta, fmaxf(x, 0.f));
 }
 
 // Byte offset of the 16-byte chunk holding (row, k..k+7) inside an A image of kTileM rows.

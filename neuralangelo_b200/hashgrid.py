@@ -108,6 +108,33 @@ def scatter_taps_planes(desc, x, unit_map, active_levels, tap_offsets, dout, dta
     return dtable
 
 
+def encode_taps_strided(desc, table, x, unit_map, active_levels, tap_offsets, out, point_stride, tap_stride, level_stride):
+    """out[t * tap_stride + l * level_stride + n * point_stride + f] (float offsets into `out`) = feature f of level l
+    at x[n] + tap_offsets[t]; the caller owns the layout (e.g. the chunk planes the SDF MLP reads)."""
+    _lib.require_cuda(table, x, out)
+    x = _as_points(x)
+    taps, n_taps = _taps_array(tap_offsets)
+    assert out.dtype == _F32
+    rc = _lib.lib().na_hashgrid_taps_fwd_strided(ctypes.byref(desc), _lib.ptr(table), _lib.ptr(x), x.shape[0], unit_map,
+                                                 int(active_levels), taps, n_taps, _lib.ptr(out), int(point_stride),
+                                                 int(tap_stride), int(level_stride), _lib.current_stream())
+    _lib.check(rc, "na_hashgrid_taps_fwd_strided")
+    return out
+
+
+def scatter_taps_strided(desc, x, unit_map, active_levels, tap_offsets, dout, point_stride, tap_stride, level_stride, dtable):
+    """dtable += backward of encode_taps_strided for the same layout of `dout`."""
+    _lib.require_cuda(dtable, x, dout)
+    x = _as_points(x)
+    taps, n_taps = _taps_array(tap_offsets)
+    assert dout.dtype == _F32
+    rc = _lib.lib().na_hashgrid_taps_bwd_strided(ctypes.byref(desc), _lib.ptr(x), x.shape[0], unit_map, int(active_levels),
+                                                 taps, n_taps, _lib.ptr(dout), int(point_stride), int(tap_stride),
+                                                 int(level_stride), _lib.ptr(dtable), _lib.current_stream())
+    _lib.check(rc, "na_hashgrid_taps_bwd_strided")
+    return dtable
+
+
 class _HashGridTaps(torch.autograd.Function):
     """Autograd wrapper: gradient w.r.t. the table only (numerical-gradient mode never asks for d/dx,
     modules.py:132-175; analytical mode, modules.py:117-130, is outside this path)."""

@@ -122,7 +122,46 @@ class NeuralSDF(torch.nn.Module):
         return _EncodeRows.forward(_NoCtx(), pts, enc.params.detach(), enc, self._unit_map, self._levels_in_use(),
                                    tuple(taps))
 
+    # ---- chunk planes: the layout both the hash-grid kernels and the SDF-only MLP kernel are fastest in ------------
+    def _planes_supported(self):
+        """8 features per level (one 32-byte chunk per level and point) and a level count the pipelined MLP kernel
+        takes; otherwise the row layout is used."""
+        if not self._hashgrid():
+            return False
+        desc = self.tcnn_encoding.desc
+        if desc.n_features != 8 or desc.n_levels % 4 != 0 or desc.n_levels > 16:
+            return False
+        packed = self._packed_mlp() if self.tcnn_encoding.params.is_cuda else None
+        return packed is not None and packed.n in (128, 256)
+
+    def encode_planes(self, points_flat, taps=((0.0, 0.0, 0.0),), table=None):
+        """[L+1, T*N, 8] chunk planes: plane l < L holds level l's features of point n + tap t at row t*N + n
+        (zeros for levels masked by coarse-to-fine), plane L holds xyz of that row in its first three floats."""
+        enc = self.tcnn_encoding
+        pts = points_flat.float().contiguous()
+        n, n_taps, n_levels = pts.shape[0], len(taps), enc.desc.n_levels
+        planes = torch.empty(n_levels + 1, n_taps * n, 8, dtype=torch.float32, device=pts.device)
+        hashgrid.encode_taps_strided(enc.desc, enc.params.detach() if table is None else table, pts, self._unit_map,
+                                     self._levels_in_use(), taps, planes, 8, n * 8, n_taps * n * 8)
+        xyz = planes[n_levels].view(n_taps, n, 8)
+        xyz[:, :, :3] = pts[None, :, :] + _tap_tensor(tuple(taps), pts.device)[:, None, :]
+        return planes
+
+    def sdf_planes(self, points_flat, taps=((0.0, 0.0, 0.0),)):
+        """SDF at points + taps without an autograd graph: one encode launch into chunk planes, one launch of the
+        pipelined SDF-only MLP.  Returns [T, N, 1]."""
+        planes = self.encode_planes(points_flat, taps)
+        sdf = self._packed_mlp().forward_planes(planes, planes.shape[1])
+        return sdf.view(len(taps), points_flat.shape[0], 1)
+
+    def _needs_graph(self):
+        return torch.is_grad_enabled() and (self.tcnn_encoding.params.requires_grad
+                                            or any(p.requires_grad for p in self.mlp.parameters()))
+
     def forward(self, points_3D, with_sdf=True, with_feat=True):
+        if with_sdf and not with_feat and points_3D.is_cuda and not (torch.is_grad_enabled() and points_3D.requires_grad) \
+                and self._planes_supported() and not self._needs_graph():
+            return self.sdf_planes(points_3D.reshape(-1, 3))[0].view(*points_3D.shape[:-1], 1), None
         points_enc = self.encode(points_3D)  # [...,3+LD]
         sdf, feat = self.run_mlp(points_enc, with_sdf=with_sdf, with_feat=with_feat)
         return sdf, feat  # [...,1],[...,K]
@@ -221,7 +260,10 @@ class NeuralSDF(torch.nn.Module):
         if mode != "numerical":
             raise ValueError(mode)
         eps, offsets = self._tap_offsets()
-        if self._hashgrid():
+        if self._hashgrid() and x.is_cuda and self._planes_supported() and not self._needs_graph() \
+                and not (torch.is_grad_enabled() and x.requires_grad):
+            s = [t.view(*x.shape[:-1], 1) for t in self.sdf_planes(x.reshape(-1, 3), taps=offsets).unbind(0)]
+        elif self._hashgrid():
             rows = self.encode_rows(x.reshape(-1, 3), taps=offsets)                 # [T,N,3+LD], one encode launch
             s = self.run_mlp(rows, with_sdf=True, with_feat=False)[0]                # [T,N,1], one MLP pass
             s = [t.view(*x.shape[:-1], 1) for t in s.unbind(0)]

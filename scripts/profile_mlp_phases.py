@@ -13,14 +13,15 @@ mlp = MLPforNeuralSDF([131, 256, 256], activ=get_activation("softplus", beta=100
 packed = PackedSdfMlp(mlp, 100.0)
 m = 1 << 21
 x = torch.randn(m, 131, device=dev)
+planes = torch.randn(17, m, 8, device=dev)
 L = _lib.lib()
 L.na_dev_mlp_prof.argtypes = [ctypes.c_void_p, ctypes.c_int]
 buf = (ctypes.c_ulonglong * 16)()
 for _ in range(2):
-    packed.forward(x, with_sdf=True, with_feat=False)
+    packed.forward_planes(planes, m)
 torch.cuda.synchronize()
 L.na_dev_mlp_prof(None, 1)
-packed.forward(x, with_sdf=True, with_feat=False)
+packed.forward_planes(planes, m)
 torch.cuda.synchronize()
 L.na_dev_mlp_prof(buf, 1)
 tiles = (m // 128 + 147) // 148
@@ -30,3 +31,12 @@ print("tiles per CTA", tiles)
 for i, nme in enumerate(names):
     print(f"{nme:22s} {buf[i] / tiles:9.0f} cycles/tile")
 print("compute total", sum(buf[i] for i in range(8)) / tiles, " MMA total", sum(buf[i] for i in range(8, 13)) / tiles)
+import numpy as np
+def timeit(fn, iters=5, warm=2):
+    for _ in range(warm): fn()
+    torch.cuda.synchronize(); ts = []
+    for _ in range(iters):
+        s, t = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record(); fn(); t.record(); torch.cuda.synchronize(); ts.append(s.elapsed_time(t))
+    return float(np.median(ts))
+print("planes ms (profiling build)", timeit(lambda: packed.forward_planes(planes, m)), " rows ms", timeit(lambda: packed.forward(x, with_sdf=True, with_feat=False)))

@@ -164,3 +164,40 @@ def test_fused_chain_in_training_matches_library_path(na_lib, cuda_device, golde
     for k in grads[True]:
         ref = grads[False][k]
         assert (grads[True][k] - ref).norm().item() <= 1e-4 * max(ref.norm().item(), 1e-12), k
+
+
+def test_chunk_plane_path_matches_row_path_on_the_default_config(na_lib, cuda_device):
+    """Without an autograd graph NeuralSDF.sdf / compute_gradients (default config: 16 levels x 8 features, 256-wide
+    MLP) run encode -> chunk planes -> pipelined SDF-only MLP.  Same values as the row-layout path (fused MLP on
+    [N,131] rows), with coarse-to-fine masking of the upper levels and a row count that is not a tile multiple."""
+    from neuralangelo_b200.config import default_model_config
+    from neuralangelo_b200.modules import NeuralSDF
+    torch.manual_seed(3)
+    cfg = default_model_config()
+    sdf_net = NeuralSDF(cfg.object.sdf).to(cuda_device)
+    with torch.no_grad():
+        sdf_net.tcnn_encoding.params.uniform_(-0.05, 0.05)          # trained-table-sized features
+        for lin in sdf_net.mlp.linears:
+            lin.weight_v.add_(torch.randn_like(lin.weight_v) * 0.02)
+    sdf_net.warm_up_end = 0
+    sdf_net.set_active_levels(current_iter=7 * cfg.object.sdf.encoding.coarse2fine.step)   # 7 of 16 levels active
+    sdf_net.set_normal_epsilon()
+    assert sdf_net._planes_supported()
+    pts = (torch.rand(3, 137, 3, generator=torch.Generator().manual_seed(1)) * 2 - 1).to(cuda_device)
+    _, offsets = sdf_net._tap_offsets()
+    with torch.no_grad():
+        got = sdf_net.sdf_planes(pts.reshape(-1, 3), taps=offsets)                              # [T,N,1]
+        rows = sdf_net.encode_rows(pts.reshape(-1, 3), taps=offsets)
+        want = sdf_net.run_mlp(rows, with_sdf=True, with_feat=False)[0]
+        torch.testing.assert_close(got, want, rtol=0, atol=2e-6)
+        # the public entry points take the plane path and agree with it
+        torch.testing.assert_close(sdf_net.sdf(pts), sdf_net.sdf_planes(pts.reshape(-1, 3))[0].view(3, 137, 1), rtol=0, atol=0)
+        grad, hess = sdf_net.compute_gradients(pts, training=True, sdf=sdf_net.sdf(pts))
+    rows_c = sdf_net.encode_rows(pts.reshape(-1, 3), taps=offsets)                              # graph path (rows)
+    s = sdf_net.run_mlp(rows_c, with_sdf=True, with_feat=False)[0].detach()
+    eps = sdf_net.normal_eps / np.sqrt(3) if cfg.object.sdf.gradient.taps == 4 else sdf_net.normal_eps
+    assert grad.shape == (3, 137, 3) and torch.isfinite(grad).all() and torch.isfinite(hess).all()
+    if cfg.object.sdf.gradient.taps == 4:
+        k = torch.tensor([[1., -1, -1], [-1, -1, 1], [-1, 1, -1], [1, 1, 1]], device=cuda_device)
+        want_grad = sum(k[i] * s[i] for i in range(4)) / (4 * eps)
+        torch.testing.assert_close(grad.reshape(-1, 3), want_grad, rtol=0, atol=2e-6 / eps)
