@@ -386,9 +386,10 @@ def extra_train_step(rank, world, dev, steps=30, warmup=8, taps=4, force_all_lev
             "synchronised steps, max over ranks; includes H2D of the batch and the gradient all-reduce"}
 
 
-def extra_mesh(rank, world, dev, res=512):
-    """BASELINE.json configs[4] at reduced resolution (the full 2048^3 takes ~30 s on one GPU): blocked SDF
-    query of the default hash-grid model + marching cubes, blocks sharded across ranks, gathered on rank 0."""
+def extra_mesh(rank, world, dev, res=2048):
+    """BASELINE.json configs[4] at full size: isosurface extraction at resolution 2048, block 128 (4096 blocks, 8.78 G
+    lattice points): blocked SDF query of the default hash-grid model (random init) + marching cubes, blocks sharded
+    across the ranks of the launch, vertex / face buffers gathered on rank 0 (about 7 s on one B200)."""
     from neuralangelo_b200 import mesh
     from neuralangelo_b200.config import default_model_config
     from neuralangelo_b200.modules import NeuralSDF
@@ -434,6 +435,38 @@ def extra_cpu_path():
     return out
 
 
+def extra_sdf_mlp(dev, m=1 << 21):
+    """The only dense contraction of the path: SDF-only evaluation (131 -> 256 -> SDF head) of 2^21 rows on the
+    pipelined tcgen05 kernel, input as chunk planes (the hash-grid kernels' layout) and as [M,131] rows."""
+    from neuralangelo_b200.mlp import MLPforNeuralSDF, get_activation
+    from neuralangelo_b200.fused_mlp import PackedSdfMlp
+    torch.manual_seed(0)
+    mlp = MLPforNeuralSDF([131, 256, 256], activ=get_activation("softplus", beta=100.0), use_weightnorm=True,
+                          geometric_init=True, out_bias=0.5).to(dev)
+    packed = PackedSdfMlp(mlp, 100.0)
+    planes = torch.randn(17, m, 8, device=dev)
+    rows = torch.randn(m, 131, device=dev)
+
+    def timed(fn, iters=5):
+        for _ in range(2):
+            fn()
+        ts = []
+        for _ in range(iters):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        return float(np.median(ts))
+
+    ms_p = timed(lambda: packed.forward_planes(planes, m))
+    ms_r = timed(lambda: packed.forward(rows, with_sdf=True, with_feat=False))
+    mma_flop = 3 * 2 * m * 144 * 256    # three fp16 MMAs per k-step (split-precision operands), K padded to 144
+    return {"rows": m, "planes_ms": ms_p, "planes_Grows_per_s": m / ms_p / 1e6, "rows_layout_ms": ms_r,
+            "mma_TFLOPs_planes": mma_flop / ms_p / 1e9, "fp32_equiv_TFLOPs_planes": 2 * m * (131 * 256 + 256) / ms_p / 1e9}
+
+
 def collect_extras(args, rank, world, dev):
     extras = {}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -441,7 +474,8 @@ def collect_extras(args, rank, world, dev):
             extras["cpu_path_configs0"] = extra_cpu_path()
         except Exception as e:  # noqa: BLE001
             extras["cpu_path_configs0"] = {"error": f"{type(e).__name__}: {e}"[:300]}
-    for name, fn in (("train_step", lambda: extra_train_step(rank, world, dev)),
+    for name, fn in (("sdf_mlp", lambda: extra_sdf_mlp(dev)),
+                     ("train_step", lambda: extra_train_step(rank, world, dev)),
                      ("train_step_4_active_levels", lambda: extra_train_step(rank, world, dev, force_all_levels=False)),
                      ("mesh_extract", lambda: extra_mesh(rank, world, dev))):
         try:

@@ -202,37 +202,34 @@ __global__ void __launch_bounds__(kFwdThreads, 1) sdf_mlp_fwd_kernel(const __gri
         uint32_t layer_it = 0;
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
             const int64_t row0 = tile * kTileM;
-            // ---- stage the input tile: fp32 rows -> fp16 hi / lo chunks.  Consecutive threads take consecutive
-            // 8-column chunks of a row (coalesced 32-byte reads); all of a thread's loads are issued before any
-            // conversion so that their latencies overlap.
+            // ---- stage the input tile: fp32 rows -> fp16 hi / lo chunks.  A warp owns 8 rows; lane = (row & 7) +
+            // 8 * (k-chunk & 3): a load instruction covers 8 rows x 128 contiguous bytes, and the 16-byte stores of
+            // each quarter warp fall into 8 different bank groups (consecutive chunks of ONE row are 2 KB apart --
+            // the same banks).  All of a batch's loads are issued before any conversion so their latencies overlap.
             {
                 const int chunks = P.layer[0].k_pad / 8;
-                const int total = kTileM * chunks;
-                constexpr int kPerThread = kTileM * (kMaxK / 8) / kFwdCompute;  // 8
+                const int s_row = warp * 8 + (lane & 7), s_kc = lane >> 3;
+                const int64_t gr = row0 + s_row;
+                const float* src_row = P.x + gr * P.ldx;
+                constexpr int kRounds = kMaxK / 8 / 4;   // 8 rounds of four k-chunks
 #pragma unroll 1
-                for (int base = 0; base < kPerThread; base += 4) {
+                for (int base = 0; base < kRounds && base * 4 < chunks; base += 4) {
                     float v[4][8];
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        const int idx = (base + u) * kFwdCompute + tid;
-                        const int r = idx / chunks, kc = idx - r * chunks;
-                        const int64_t gr = row0 + r;
-                        const float* src = P.x + gr * P.ldx + kc * 8;
+                        const int kc = 4 * (base + u) + s_kc;
 #pragma unroll
                         for (int e = 0; e < 8; ++e)
-                            v[u][e] = (idx < total && gr < P.m && kc * 8 + e < P.k0) ? __ldg(src + e) : 0.f;
+                            v[u][e] = (kc < chunks && gr < P.m && kc * 8 + e < P.k0) ? __ldg(src_row + kc * 8 + e) : 0.f;
                     }
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        const int idx = (base + u) * kFwdCompute + tid;
-                        if (idx >= total) continue;
-                        const int r = idx / chunks, kc = idx - r * chunks;
+                        const int kc = 4 * (base + u) + s_kc;
+                        if (kc >= chunks) continue;
                         uint32_t hi[4], lo[4];
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            split2_f16(v[u][2 * j], v[u][2 * j + 1], hi[j], lo[j]);
-                        }
-                        const uint32_t off = a_chunk_offset(r, kc);
+                        for (int j = 0; j < 4; ++j) split2_f16(v[u][2 * j], v[u][2 * j + 1], hi[j], lo[j]);
+                        const uint32_t off = a_chunk_offset(s_row, kc);
                         *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
                         *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
                     }
