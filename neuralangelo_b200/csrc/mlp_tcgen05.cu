@@ -541,7 +541,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         const float p = fmaf(__uint_as_float(rc[j + e]), kLoInv, __uint_as_float(rm[j + e])) + bb[e];
-                        act[j + e] = softplus(p, P.beta, inv_beta);
+                        act[j + e] = (e & 1) ? softplus_poly(p, P.beta, inv_beta) : softplus(p, P.beta, inv_beta);
                         dot = fmaf(act[j + e], hh[e], dot);
                     }
                 }

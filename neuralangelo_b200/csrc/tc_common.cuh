@@ -109,6 +109,24 @@ __device__ __forceinline__ float softplus(float x, float beta, float inv_beta) {
     return fmaf(l, 0.6931471805599453f * inv_beta, fmaxf(x, 0.f));
 }
 
+// Same function with the logarithm on the FMA pipe: log1p(u) = u * P7(u) on u = exp(-|beta x|) in (0, 1] (Chebyshev
+// interpolant, |error| < 2e-7 absolute evaluated in fp32, i.e. < 2e-9 on the activation for beta = 100 -- the class of
+// lg2.approx).  One MUFU per element instead of two: the pipelined SDF kernel's epilogue is MUFU-bound, so it
+// alternates the two forms to balance the special-function and FMA pipes.
+__device__ __forceinline__ float softplus_poly(float x, float beta, float inv_beta) {
+    float u;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(u) : "f"(fabsf(x) * (beta * -1.4426950408889634f)));
+    float p = -8.371152549e-03f;
+    p = fmaf(p, u, 4.349389982e-02f);
+    p = fmaf(p, u, -1.068500286e-01f);
+    p = fmaf(p, u, 1.768747670e-01f);
+    p = fmaf(p, u, -2.447477418e-01f);
+    p = fmaf(p, u, 3.327192838e-01f);
+    p = fmaf(p, u, -4.999717452e-01f);
+    p = fmaf(p, u, 9.999997808e-01f);
+    return fmaf(p * u, inv_beta, fmaxf(x, 0.f));
+}
+
 // Byte offset of the 16-byte chunk holding (row, k..k+7) inside an A image of kTileM rows.
 __device__ __forceinline__ uint32_t a_chunk_offset(int row, int kchunk) {
     return (uint32_t)kchunk * (kTileM / 8 * 128) + (uint32_t)(row >> 3) * 128 + (uint32_t)(row & 7) * 16;

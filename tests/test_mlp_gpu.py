@@ -52,7 +52,8 @@ def test_pipelined_sdf_only_forward(na_lib, cuda_device, k0, n, m):
     """SDF-only evaluation takes the pipelined kernel (resident weights, two accumulator units, register-prefetched
     input tiles): a single short tile, ragged last tiles, several tiles per CTA, packed and strided rows.
     Reference: float64 module on the CPU; and the staged two-layer kernel, whose first layer runs the same sequence
-    of MMAs per element (bit-equal hidden activations)."""
+    of MMAs per element (hidden activations equal up to the log1p evaluation: the pipelined epilogue alternates
+    lg2.approx with an FMA-pipe polynomial)."""
     from neuralangelo_b200.fused_mlp import PackedSdfMlp
     mlp = _mlp(k0, n, seed=k0 + n + 1)
     g = torch.Generator().manual_seed(m)
@@ -69,7 +70,7 @@ def test_pipelined_sdf_only_forward(na_lib, cuda_device, k0, n, m):
     sdf_s, _, hidden_s = packed.forward(buf[:, 1:], with_sdf=True, with_feat=False, with_hidden=True)
     assert torch.equal(hidden, hidden_s) and torch.equal(sdf, sdf_s)
     sdf_2, _, hidden_2 = packed.forward(xp, with_sdf=True, with_feat=True, with_hidden=True)   # staged kernel
-    assert torch.equal(hidden, hidden_2)
+    assert (hidden - hidden_2).abs().max().item() <= 1e-7 * max(hidden_2.abs().max().item(), 1.0)   # log1p: polynomial vs lg2
     assert (sdf - sdf_2).abs().max().item() <= 1e-6 * max(ref_sdf.abs().max().item(), 1.0)  # head sum order differs
     assert torch.all(guard == 7.0)
     # a second launch on the same stream reproduces the first bit for bit
