@@ -227,12 +227,30 @@ def run_ours(args, rank, local_rank, world):
             ev[2].record()
         launches[0] += 2
 
-    def step_e2e():
-        pts_dev.copy_(pts_host, non_blocking=True)
-        step(pts_dev)
-        res = torch.cat([out[0, :, 0, :].reshape(-1), dtable[:262144].sum().reshape(1)])
-        result_host.copy_(res, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+    # End-to-end form: the points of every step start in pinned HOST memory and the step's result summary ends there.
+    # The copies are double-buffered on a copy stream, so step k+1's 50 MB upload runs under step k's kernels; the
+    # host blocks once, after the last step's read-back.
+    copy_stream = torch.cuda.Stream(device=dev)
+    pts_dev2 = [pts_dev, torch.empty_like(pts_dev)]
+    result_host2 = [result_host, torch.empty(129, dtype=torch.float32).pin_memory()]
+    copied = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+
+    def run_e2e(n_steps):
+        cur = torch.cuda.current_stream()
+        for k in range(n_steps):
+            b = k & 1
+            with torch.cuda.stream(copy_stream):
+                if k >= 2:
+                    copy_stream.wait_event(consumed[b])
+                pts_dev2[b].copy_(pts_host, non_blocking=True)
+                copied[b].record(copy_stream)
+            cur.wait_event(copied[b])
+            step(pts_dev2[b])
+            consumed[b].record(cur)
+            res = torch.cat([out[0, :, 0, :].reshape(-1), dtable[:262144].sum().reshape(1)])
+            result_host2[b].copy_(res, non_blocking=True)
+        cur.synchronize()
 
     def barrier():
         if world > 1:
@@ -257,12 +275,10 @@ def run_ours(args, rank, local_rank, world):
     fwd_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in kernel_events]))
     bwd_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in kernel_events]))
 
-    for _ in range(max(1, args.warmup // 2)):
-        step_e2e()
+    run_e2e(max(2, args.warmup // 2))
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step_e2e()
+    run_e2e(args.steps)
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3
 
@@ -270,7 +286,7 @@ def run_ours(args, rank, local_rank, world):
         t = torch.tensor([elapsed_ms, e2e_ms], device=dev, dtype=torch.float64)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         elapsed_ms, e2e_ms = t.tolist()
-    del out, dout, dtable, table, pts_dev
+    del out, dout, dtable, table, pts_dev, pts_dev2
     torch.cuda.empty_cache()
     if rank != 0:
         if not args.no_extras:
@@ -295,7 +311,8 @@ def run_ours(args, rank, local_rank, world):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(),
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": N_POINTS * 12,
-                "d2h_bytes_per_step": 129 * 4, "ms_per_step": e2e_ms / args.steps},
+                "d2h_bytes_per_step": 129 * 4, "ms_per_step": e2e_ms / args.steps,
+                "pipelining": "double-buffered pinned->device uploads on a copy stream; one host sync after the last read-back"},
         "gpu_launches": gpu_launches,
         "clocks": clocks.summary(),
         "roofline": {"bound": "hbm", "kernel": dominant[0], "achieved": achieved, "peak": peaks["hbm_gbs"],
@@ -463,8 +480,60 @@ def extra_sdf_mlp(dev, m=1 << 21):
     ms_p = timed(lambda: packed.forward_planes(planes, m))
     ms_r = timed(lambda: packed.forward(rows, with_sdf=True, with_feat=False))
     mma_flop = 3 * 2 * m * 144 * 256    # three fp16 MMAs per k-step (split-precision operands), K padded to 144
-    return {"rows": m, "planes_ms": ms_p, "planes_Grows_per_s": m / ms_p / 1e6, "rows_layout_ms": ms_r,
+    peaks = measured_peaks()[0]
+    return {"mma_frac_of_measured_dense_bf16_peak": mma_flop / ms_p / 1e9 / peaks["bf16_tflops"],
+            "rows": m, "planes_ms": ms_p, "planes_Grows_per_s": m / ms_p / 1e6, "rows_layout_ms": ms_r,
             "mma_TFLOPs_planes": mma_flop / ms_p / 1e9, "fp32_equiv_TFLOPs_planes": 2 * m * (131 * 256 + 256) / ms_p / 1e9}
+
+
+def extra_composite(dev, log2_rays=20):
+    """Compositing microbenchmark: the fused NeuS renderer (alphas -> transmittance -> weights ->
+    composites, object + background samples) forward and backward on 2^20 rays x (128 + 32) samples; achieved GB/s of
+    ALGORITHMIC bytes and the fraction of the measured HBM peak."""
+    from neuralangelo_b200 import render
+    R, N, NB = 1 << log2_rays, 128, 32
+    g = torch.Generator(device=dev).manual_seed(0)
+    ray = torch.nn.functional.normalize(torch.randn(1, R, 3, device=dev, generator=g), dim=-1)
+    dists = torch.sort(torch.rand(1, R, N, 1, device=dev, generator=g) * 2 + 1, dim=2).values
+    sdf = ((2.0 - dists) * 0.4 + 0.02 * torch.randn(1, R, N, 1, device=dev, generator=g)).requires_grad_(True)
+    grad = (-ray[:, :, None, :] + 0.3 * torch.randn(1, R, N, 3, device=dev, generator=g)).requires_grad_(True)
+    rgb = torch.rand(1, R, N, 3, device=dev, generator=g).requires_grad_(True)
+    dens = torch.rand(1, R, NB, device=dev, generator=g).requires_grad_(True)
+    dbg = torch.sort(torch.rand(1, R, NB, 1, device=dev, generator=g) * 10 + 3.2, dim=2).values
+    rgbb = torch.rand(1, R, NB, 3, device=dev, generator=g).requires_grad_(True)
+    far = dists[:, :, -1:, :] + 0.1
+    s_var = torch.tensor(3.0, device=dev, requires_grad=True)
+
+    def timed(fn, iters=5):
+        for _ in range(2):
+            fn()
+        ts = []
+        for _ in range(iters):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        return float(np.median(ts))
+
+    kw = dict(dist_far=far, densities_bg=dens, dists_bg=dbg, rgbs_bg=rgbb, want_weights=False)
+
+    def fwd():
+        with torch.no_grad():
+            render.neus_render(ray, sdf, grad, dists, s_var, rgb, **kw)
+
+    peak = measured_peaks()[0]["hbm_gbs"]
+    b_in = N * 32 + NB * 20 + 12 + 4          # per ray: sdf 4 + grad 12 + dist 4 + rgb 12 per object sample; 20 per bg sample
+    ms_f = timed(fwd)
+    by_f = R * (b_in + 16)
+    out, _, _ = render.neus_render(ray, sdf, grad, dists, s_var, rgb, **kw)
+    d_rgb = torch.randn_like(out)
+    ms_b = timed(lambda: torch.autograd.grad(out, [sdf, grad, rgb, dens, rgbb, s_var], d_rgb, retain_graph=True))
+    by_b = R * (b_in + 12 + N * 28 + NB * 16)  # inputs re-read + d_rgb; d_sdf, d_grad, d_rgb, d_dens, d_rgb_bg written
+    return {"rays": R, "samples": [N, NB],
+            "fwd": {"ms": ms_f, "GBps": by_f / ms_f / 1e6, "frac_of_hbm_peak": by_f / ms_f / 1e6 / peak},
+            "bwd": {"ms": ms_b, "GBps": by_b / ms_b / 1e6, "frac_of_hbm_peak": by_b / ms_b / 1e6 / peak}}
 
 
 def collect_extras(args, rank, world, dev):
@@ -475,6 +544,7 @@ def collect_extras(args, rank, world, dev):
         except Exception as e:  # noqa: BLE001
             extras["cpu_path_configs0"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     for name, fn in (("sdf_mlp", lambda: extra_sdf_mlp(dev)),
+                     ("composite", lambda: extra_composite(dev)),
                      ("train_step", lambda: extra_train_step(rank, world, dev)),
                      ("train_step_4_active_levels", lambda: extra_train_step(rank, world, dev, force_all_levels=False)),
                      ("mesh_extract", lambda: extra_mesh(rank, world, dev))):
