@@ -34,7 +34,7 @@ def _fingerprint():
     files = sources() + sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh"))
     files += [os.path.join(INCLUDE, f) for f in sorted(os.listdir(INCLUDE))]
     for f in files:
-        h.update(f.encode())
+        h.update(os.path.basename(f).encode())   # names, not absolute paths: the tree may be mounted elsewhere
         with open(f, "rb") as fh:
             h.update(fh.read())
     h.update(" ".join(NVCC_FLAGS).encode())
@@ -49,14 +49,28 @@ def is_current():
 
 
 def build(force=False, verbose=True):
-    """Compile every .cu under csrc/ into libna_b200.so.  Returns the library path."""
+    """Compile every .cu under csrc/ into libna_b200.so.  Returns the library path.  Safe to call from several
+    processes at once (the ranks of one launch): an exclusive file lock serialises them and the late comers find
+    the library current."""
     if not force and is_current():
         return LIB_PATH
+    import fcntl
+    obj_dir = os.path.join(PKG_DIR, "build")
+    os.makedirs(obj_dir, exist_ok=True)
+    with open(os.path.join(obj_dir, ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and is_current():
+                return LIB_PATH
+            return _build_locked(obj_dir, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(obj_dir, verbose):
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
         raise RuntimeError("nvcc not found: cannot build libna_b200.so")
-    obj_dir = os.path.join(PKG_DIR, "build")
-    os.makedirs(obj_dir, exist_ok=True)
     objs = []
     log = []
     for src in sources():
@@ -68,11 +82,13 @@ def build(force=False, verbose=True):
             sys.stderr.write(r.stdout + r.stderr)
             raise RuntimeError(f"nvcc failed on {src}")
         objs.append(obj)
-    cmd = [nvcc, "-shared", "-o", LIB_PATH, *objs, "-lcudart"]
+    tmp_lib = LIB_PATH + ".tmp"
+    cmd = [nvcc, "-shared", "-o", tmp_lib, *objs, "-lcudart"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
         raise RuntimeError("link failed")
+    os.replace(tmp_lib, LIB_PATH)
     with open(os.path.join(obj_dir, "ptxas.log"), "w") as fh:
         fh.write("\n".join(log))
     with open(STAMP_PATH, "w") as fh:
