@@ -601,10 +601,17 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
             if (head && P.sdf_out) {
                 float* part = head_partial + (q & 1) * 4 * kTileM;
                 part[group * kTileM + row] = dot;   // groups without columns contribute 0
-                asm volatile("bar.sync 1, %0;" ::"n"(kPipeCompute) : "memory");
-                if (group == 0 && row0 + row < P.m)
-                    P.sdf_out[row0 + row] = __ldg(P.b_head) + part[row] + part[kTileM + row] + part[2 * kTileM + row] +
-                                            part[3 * kTileM + row];
+                // groups 1-3 only announce their partial sums and move on; group 0 waits for them and writes the SDF.
+                // The partial buffer alternates with the tile parity, and a group cannot be two tiles ahead of
+                // group 0 (a_ready needs every compute thread), so the slot read here is never being rewritten.
+                if (group != 0) {
+                    asm volatile("bar.arrive 1, %0;" ::"n"(kPipeCompute) : "memory");
+                } else {
+                    asm volatile("bar.sync 1, %0;" ::"n"(kPipeCompute) : "memory");
+                    if (row0 + row < P.m)
+                        P.sdf_out[row0 + row] = __ldg(P.b_head) + part[row] + part[kTileM + row] + part[2 * kTileM + row] +
+                                                part[3 * kTileM + row];
+                }
             }
             PROF(7);
         }

@@ -261,7 +261,7 @@ def _gather_to_rank0(t, rank, world, device):
 
 
 @torch.no_grad()
-def extract_mesh(sdf_func, bounds, intv, block_res=64, texture_func=None, filter_lcc=False, device=None):
+def extract_mesh(sdf_func, bounds, intv, block_res=64, texture_func=None, filter_lcc=False, device=None, stats=None):
     """mesh.py:24-49.  Blocks are dealt round-robin to ranks exactly as DistributedSampler(shuffle=False)
     does (block idx = rank, rank + W, ...); each block's lattice is built on the device, queried, meshed
     and filtered there; rank 0 receives the vertex / face buffers and concatenates them."""
@@ -269,6 +269,8 @@ def extract_mesh(sdf_func, bounds, intv, block_res=64, texture_func=None, filter
     device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
     grid = LatticeGrid(bounds, intv=intv, block_res=block_res)
     v_parts, f_parts, c_parts, v_total = [], [], [], 0
+    import time
+    t_start = time.perf_counter()
     for idx in range(rank, len(grid), world):
         gx, gy, gz = (g.to(device) for g in grid.block_axes(idx))
         xyz = torch.stack(torch.meshgrid(gx, gy, gz, indexing="ij"), dim=-1)
@@ -283,6 +285,10 @@ def extract_mesh(sdf_func, bounds, intv, block_res=64, texture_func=None, filter
     F = torch.cat(f_parts) if f_parts else torch.zeros(0, 3, dtype=torch.long, device=device)
     textured = texture_func is not None
     C = (torch.cat(c_parts) if c_parts else torch.zeros(0, 3, dtype=torch.uint8, device=device)) if textured else None
+    if stats is not None:   # optional phase timing (`stats` is a dict the caller passes in): seconds on this rank
+        torch.cuda.synchronize(device)
+        stats["blocks_s"] = time.perf_counter() - t_start
+        t_start = time.perf_counter()
     if world > 1:
         Vs, v_sizes = _gather_to_rank0(V, rank, world, device)
         Fs, _ = _gather_to_rank0(F, rank, world, device)
@@ -293,4 +299,11 @@ def extract_mesh(sdf_func, bounds, intv, block_res=64, texture_func=None, filter
         V = torch.cat(Vs)
         F = torch.cat([f + int(o) for f, o in zip(Fs, offs)])
         C = torch.cat(Cs) if textured else None
-    return Mesh(V.cpu().numpy(), F.cpu().numpy(), None if C is None else C.cpu().numpy())
+    if stats is not None:
+        torch.cuda.synchronize(device)
+        stats["gather_s"] = time.perf_counter() - t_start
+        t_start = time.perf_counter()
+    out = Mesh(V.cpu().numpy(), F.cpu().numpy(), None if C is None else C.cpu().numpy())
+    if stats is not None:
+        stats["host_mesh_s"] = time.perf_counter() - t_start
+    return out

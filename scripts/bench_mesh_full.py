@@ -19,7 +19,9 @@ fn = lambda x: -net.sdf(x)
 mesh.extract_mesh(fn, bounds, intv=2.0 / 128, block_res=128)
 if world > 1: dist.barrier()
 torch.cuda.synchronize(); t0 = time.perf_counter()
-m = mesh.extract_mesh(fn, bounds, intv=2.0 / res, block_res=128)
+stats = {}
+m = mesh.extract_mesh(fn, bounds, intv=2.0 / res, block_res=128, stats=stats)
+print('rank', rank, {k: round(v, 3) for k, v in stats.items()}, flush=True)
 torch.cuda.synchronize(); dt = time.perf_counter() - t0
 if world > 1:
     t = torch.tensor([dt], device=dev, dtype=torch.float64); dist.all_reduce(t, op=dist.ReduceOp.MAX); dt = float(t)
