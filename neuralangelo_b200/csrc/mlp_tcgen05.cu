@@ -602,12 +602,13 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
                 float* part = head_partial + (q & 1) * 4 * kTileM;
                 part[group * kTileM + row] = dot;   // groups without columns contribute 0
                 // groups 1-3 only announce their partial sums and move on; group 0 waits for them and writes the SDF.
-                // The partial buffer alternates with the tile parity, and a group cannot be two tiles ahead of
-                // group 0 (a_ready needs every compute thread), so the slot read here is never being rewritten.
+                // A group can be at most one tile ahead of group 0 (d_empty / a_ready need every compute thread), so
+                // both the partial buffer and the named barrier alternate with the tile parity.
+                const uint32_t bar_id = 1u + (q & 1u);
                 if (group != 0) {
-                    asm volatile("bar.arrive 1, %0;" ::"n"(kPipeCompute) : "memory");
+                    asm volatile("bar.arrive %0, %1;" ::"r"(bar_id), "n"(kPipeCompute) : "memory");
                 } else {
-                    asm volatile("bar.sync 1, %0;" ::"n"(kPipeCompute) : "memory");
+                    asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(kPipeCompute) : "memory");
                     if (row0 + row < P.m)
                         P.sdf_out[row0 + row] = __ldg(P.b_head) + part[row] + part[kTileM + row] + part[2 * kTileM + row] +
                                                 part[3 * kTileM + row];
