@@ -521,6 +521,10 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
             }
         };
 
+        // Half of the warp groups request a tile's rows one phase earlier than the other half (right after the
+        // conversion that frees their registers instead of at the top of the next iteration): the two bursts of
+        // load issue then overlap with the other half's epilogue arithmetic instead of stalling all sixteen warps.
+        const bool early = group >= 2;
         float dot = 0.f;
         auto epilogue = [&](int h, int64_t row0) {
             const uint32_t d_main = tmem_base + 256u * h + lane_addr, d_cross = d_main + 128u;
@@ -567,13 +571,19 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
             convert();
             fence_proxy_async();
             mbar_arrive(a_ready);
+            if (early) {
+#pragma unroll
+                for (int st = 0; st <= ROUNDS; ++st) load_step((int64_t)blockIdx.x + gridDim.x, st);
+            }
         }
         PROF_DECL(blockIdx.x == 0 && threadIdx.x == 0);
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
             const int64_t row0 = tile * kTileM;
             const int64_t next = tile + gridDim.x;
+            if (!early) {
 #pragma unroll
-            for (int st = 0; st <= ROUNDS; ++st) load_step(next, st);   // in flight during the first epilogue
+                for (int st = 0; st <= ROUNDS; ++st) load_step(next, st);   // in flight during the first epilogue
+            }
             dot = 0.f;
             PROF(0);
             mbar_wait(d_full(0), q & 1);
@@ -589,6 +599,10 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
                 convert();
                 fence_proxy_async();
                 mbar_arrive(a_ready);
+                if (early) {   // registers are free again: request the tile after the next one right away
+#pragma unroll
+                    for (int st = 0; st <= ROUNDS; ++st) load_step(next + gridDim.x, st);
+                }
                 PROF(4);
             }
             mbar_wait(d_full(1), q & 1);
