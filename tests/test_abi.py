@@ -55,3 +55,34 @@ def test_product_refuses_cpu_tensors(na_lib):
     from neuralangelo_b200 import _lib, render
     with pytest.raises(_lib.NaError):
         render.alpha_compositing_weights(torch.rand(1, 2, 3))
+
+
+def test_build_fingerprint_does_not_depend_on_the_mount_path(tmp_path):
+    """The library built in the authoring container must be recognised as current when the tree is mounted elsewhere
+    (the GPU box): the fingerprint hashes file names and contents, not absolute paths.  (Ranks of one launch used to
+    race to rebuild it; build() now also takes an exclusive lock and replaces the .so atomically.)"""
+    import importlib.util
+    import shutil
+    dst = tmp_path / "elsewhere"
+    shutil.copytree(os.path.join(ROOT, "neuralangelo_b200"), dst / "neuralangelo_b200",
+                    ignore=shutil.ignore_patterns("*.so", "*.o", "build", "__pycache__"))
+    shutil.copytree(os.path.join(ROOT, "include"), dst / "include")
+    spec = importlib.util.spec_from_file_location("build_elsewhere", dst / "neuralangelo_b200" / "build.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    from neuralangelo_b200 import build
+    assert mod._fingerprint() == build._fingerprint()
+
+
+def test_plane_entry_point_validates_its_envelope(na_lib):
+    """na_sdf_head_fwd_planes rejects shapes outside the pipelined kernel's envelope with a message (host-side checks
+    run before any device work)."""
+    import ctypes as C
+    fake = C.c_void_p(256)   # non-null, 16-byte aligned; never dereferenced: validation fails first
+    rc = na_lib.na_sdf_head_fwd_planes(fake, 8 * 128, 128, 131, 192, fake, fake, fake, 144, None, None, 100.0, None, None, 0, None)
+    assert rc != 0 and b"hidden width" in na_lib.na_last_error()
+    rc = na_lib.na_sdf_head_fwd_planes(fake, 8 * 128, 128, 19, 256, fake, fake, fake, 32, None, None, 100.0, None, None, 0, None)
+    assert rc != 0 and b"k0=19" in na_lib.na_last_error()
+    rc = na_lib.na_sdf_head_fwd_planes(fake, 8 * 100, 128, 131, 256, fake, fake, fake, 144, None, None, 100.0, None, None, 0, None)
+    assert rc != 0 and b"chunk_stride" in na_lib.na_last_error()
+    assert na_lib.na_sdf_head_fwd_planes(fake, 8 * 128, 0, 131, 256, fake, fake, fake, 144, None, None, 100.0, None, None, 0, None) == 0
