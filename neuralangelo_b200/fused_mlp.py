@@ -60,6 +60,15 @@ class PackedSdfMlp:
             # chunk-plane column order: encoding features first (one 8-wide chunk per level), xyz in the last chunk
             w0 = l0.effective_weight()
             new.update(zip(("w0p_hi", "w0p_lo"), pack_weight(torch.cat([w0[:, 3:], w0[:, :3]], dim=1), self.k0_pad)))
+            # operands of the backward products (dz1 W1, dz0 W0): transposed weights in the same packed form, and the
+            # two norms its row scaling uses -- cached here so that a training step packs once, not per call
+            w1 = l1.effective_weight()
+            w0t = torch.zeros(self.k0_pad, self.n, dtype=torch.float32, device=w0.device)
+            w0t[:self.k0] = w0.detach().float().t()
+            new.update(zip(("w0t_hi", "w0t_lo"), pack_weight(w0t, self.n)))
+            new.update(zip(("w1t_hi", "w1t_lo"), pack_weight(w1.detach().float().t().contiguous(), self.n)))
+            new["norms"] = torch.stack([w1.detach().abs().sum(dim=0).max().float(),
+                                        mlp.linear_sdf.weight.detach().abs().max().float()])
             new["b0"] = l0.bias.detach().float().contiguous()
             new["b1"] = l1.bias.detach().float().contiguous()
             new["w_head"] = mlp.linear_sdf.weight.detach().float().reshape(-1).contiguous()
@@ -113,25 +122,33 @@ class FusedSdfMlpFunction(torch.autograd.Function):
     Arguments are the EFFECTIVE weights (torch applies / differentiates the weight-norm reparametrisation)."""
 
     @staticmethod
-    def forward(ctx, rows, w0, b0, w1, b1, w_head, b_head, beta, with_feat):
+    def forward(ctx, rows, w0, b0, w1, b1, w_head, b_head, beta, with_feat, packed=None):
+        """`packed`: a PackedSdfMlp holding the CURRENT weights (NeuralSDF keeps one and refreshes it after every
+        optimiser step); without it the operands are packed here, per call."""
         m, k0 = rows.shape
         n = w0.shape[0]
         k0_pad = pad16(k0)
-        with torch.no_grad():
-            w0_hi, w0_lo = pack_weight(w0, k0_pad)
-            w1_hi, w1_lo = pack_weight(w1, n) if with_feat else (None, None)
+        if packed is not None:
+            w0_hi, w0_lo, w1_hi, w1_lo = packed.w0_hi, packed.w0_lo, packed.w1_hi, packed.w1_lo
+            b0c, b1c, whc, bhc = packed.b0, packed.b1, packed.w_head, packed.b_head
+        else:
+            with torch.no_grad():
+                w0_hi, w0_lo = pack_weight(w0, k0_pad)
+                w1_hi, w1_lo = pack_weight(w1, n) if with_feat else (None, None)
+            b0c, b1c, whc = b0.detach().float().contiguous(), b1.detach().float().contiguous(), \
+                w_head.detach().float().reshape(-1).contiguous()
+            bhc = b_head.detach().float().reshape(1).contiguous()
         dev = rows.device
         sdf = torch.empty(m, 1, dtype=torch.float32, device=dev)
         feat = torch.empty(m, n, dtype=torch.float32, device=dev) if with_feat else None
         hidden = torch.empty(m, n, dtype=torch.float32, device=dev)
-        b0c, b1c, whc = b0.detach().float().contiguous(), b1.detach().float().contiguous(), \
-            w_head.detach().float().reshape(-1).contiguous()
         rc = _L().na_sdf_mlp_fwd(ptr(rows), rows.stride(0), m, k0, n, 2 if with_feat else 1, ptr(w0_hi), ptr(w0_lo),
-                                 ptr(b0c), k0_pad, ptr(w1_hi), ptr(w1_lo), ptr(b1c), ptr(whc),
-                                 ptr(b_head.detach().float().reshape(1).contiguous()), float(beta), ptr(sdf), ptr(feat), n, ptr(hidden), n, _lib.current_stream())
+                                 ptr(b0c), k0_pad, ptr(w1_hi) if with_feat else None, ptr(w1_lo) if with_feat else None,
+                                 ptr(b1c), ptr(whc), ptr(bhc), float(beta), ptr(sdf), ptr(feat), n, ptr(hidden), n,
+                                 _lib.current_stream())
         _lib.check(rc, "na_sdf_mlp_fwd")
         ctx.save_for_backward(rows, hidden, feat if with_feat else hidden, w0, w1, whc)
-        ctx.beta, ctx.with_feat = float(beta), with_feat
+        ctx.beta, ctx.with_feat, ctx.packed = float(beta), with_feat, packed
         if not with_feat:
             feat = torch.empty(0, device=dev)
             ctx.mark_non_differentiable(feat)
@@ -146,20 +163,28 @@ class FusedSdfMlpFunction(torch.autograd.Function):
         dev = rows.device
         two = ctx.with_feat and d_feat is not None
         d_sdf = d_sdf.float().contiguous().reshape(-1) if d_sdf is not None else torch.zeros(m, device=dev)
+        packed = ctx.packed
         with torch.no_grad():
-            w0t = torch.zeros(k0_pad, n, dtype=torch.float32, device=dev)
-            w0t[:k0] = w0.detach().float().t()
-            w0t_hi, w0t_lo = pack_weight(w0t, n)
+            if packed is not None:
+                w0t_hi, w0t_lo = packed.w0t_hi, packed.w0t_lo
+            else:
+                w0t = torch.zeros(k0_pad, n, dtype=torch.float32, device=dev)
+                w0t[:k0] = w0.detach().float().t()
+                w0t_hi, w0t_lo = pack_weight(w0t, n)
             if two:
                 d_feat = d_feat.float().contiguous()
-                w1t_hi, w1t_lo = pack_weight(w1.detach().float().t().contiguous(), n)
+                w1t_hi, w1t_lo = (packed.w1t_hi, packed.w1t_lo) if packed is not None else \
+                    pack_weight(w1.detach().float().t().contiguous(), n)
                 bound = d_feat.abs().amax(dim=1).contiguous()
-                colsum = w1.detach().abs().sum(dim=0).max().reshape(1)
+                colsum = w1.detach().abs().sum(dim=0).max().reshape(1) if packed is None else None
                 dz1 = torch.empty(m, n, dtype=torch.float32, device=dev)
             else:
                 w1t_hi = w1t_lo = bound = dz1 = None
-                colsum = torch.zeros(1, device=dev)
-            norms = torch.cat([colsum.float(), w_head.abs().max().reshape(1)])   # device scalars: no host sync
+                colsum = torch.zeros(1, device=dev) if packed is None else None
+            if packed is not None:   # the two-layer bound is also valid (merely looser) for SDF-only rows
+                norms = packed.norms
+            else:
+                norms = torch.cat([colsum.float(), w_head.abs().max().reshape(1)])   # device scalars: no host sync
             dz0 = torch.empty(m, n, dtype=torch.float32, device=dev)
             dx = torch.empty(m, k0, dtype=torch.float32, device=dev)
             rc = _L().na_sdf_mlp_bwd(m, n, k0, k0_pad, 1 if two else 0, ptr(d_sdf), ptr(d_feat) if two else None,
@@ -172,20 +197,32 @@ class FusedSdfMlpFunction(torch.autograd.Function):
             prev = torch.backends.cuda.matmul.allow_tf32
             torch.backends.cuda.matmul.allow_tf32 = True
             try:
-                dw0 = dz0.t() @ rows
+                dw0 = _tn_matmul(dz0, rows)
                 db0 = dz0.sum(dim=0)
-                dw1 = dz1.t() @ hidden if two else None
+                dw1 = _tn_matmul(dz1, hidden) if two else None
                 db1 = dz1.sum(dim=0) if two else None
                 dwh = (d_sdf[None, :] @ hidden)
                 dbh = d_sdf.sum().reshape(1)
             finally:
                 torch.backends.cuda.matmul.allow_tf32 = prev
-        return dx, dw0, db0, dw1, db1, dwh, dbh, None, None
+        return dx, dw0, db0, dw1, db1, dwh, dbh, None, None, None
 
 
-def fused_sdf_mlp(mlp, rows, beta, with_sdf=True, with_feat=True):
+def _tn_matmul(a, b):
+    """a^T b for tall operands a [M,p], b [M,q] (M >> p, q: a weight gradient, a reduction over all rows).  As one
+    GEMM the output has only a handful of tiles and the library runs it on a few SMs (measured 312 us for
+    M = 262144, p = 256, q = 131); split along M into independent batched products it fills the GPU."""
+    m = a.shape[0]
+    for parts in (64, 32, 16, 8):
+        if m % parts == 0 and m // parts >= 1024:
+            return torch.bmm(a.view(parts, m // parts, a.shape[1]).transpose(1, 2),
+                             b.reshape(parts, m // parts, b.shape[1])).sum(dim=0)
+    return a.t() @ b
+
+
+def fused_sdf_mlp(mlp, rows, beta, with_sdf=True, with_feat=True, packed=None):
     """Autograd-aware fused evaluation of an MLPforNeuralSDF (one hidden layer) on rows [M,K0]."""
     l0, l1 = mlp.linears
     sdf, feat = FusedSdfMlpFunction.apply(rows, l0.effective_weight(), l0.bias, l1.effective_weight(), l1.bias,
-                                          mlp.linear_sdf.weight, mlp.linear_sdf.bias, beta, with_feat)
+                                          mlp.linear_sdf.weight, mlp.linear_sdf.bias, beta, with_feat, packed)
     return (sdf if with_sdf else None), (feat if with_feat else None)

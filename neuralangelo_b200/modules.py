@@ -206,7 +206,7 @@ class NeuralSDF(torch.nn.Module):
             flat = flat.float().contiguous()
         if needs_graph:   # tcgen05 forward + input-gradient chain, weight gradients through torch (fused_mlp.py)
             from .fused_mlp import fused_sdf_mlp
-            sdf, feat = fused_sdf_mlp(self.mlp, flat, packed.beta, with_sdf=with_sdf, with_feat=with_feat)
+            sdf, feat = fused_sdf_mlp(self.mlp, flat, packed.beta, with_sdf=with_sdf, with_feat=with_feat, packed=packed)
         else:
             sdf, feat = packed.forward(flat, with_sdf=with_sdf, with_feat=with_feat)
         lead = rows.shape[:-1]

@@ -123,7 +123,7 @@ def test_finite_difference_gradient_quality(na_lib, cuda_device):
     assert err <= 2e-3 * max(ref.abs().max().item(), 1.0), err
 
 
-@pytest.mark.parametrize("with_feat,m", [(True, 700), (False, 1300)])
+@pytest.mark.parametrize("with_feat,m", [(True, 700), (False, 1300), (True, 8192)])   # 8192: split-K weight gradients
 def test_fused_sdf_mlp_backward(na_lib, cuda_device, with_feat, m):
     """Gradients w.r.t. the input rows and every parameter (through weight norm) vs float64 autograd.
     Upstream gradients span 1e-9 .. 1e-3 per row (what a mean-reduced loss produces) to exercise the row scaling."""
