@@ -9,6 +9,7 @@ import torch
 
 from . import _lib
 from ._lib import ptr
+from .mlp import tn_matmul
 
 _L = _lib.lib
 LO_SCALE = 2048.0
@@ -197,27 +198,15 @@ class FusedSdfMlpFunction(torch.autograd.Function):
             prev = torch.backends.cuda.matmul.allow_tf32
             torch.backends.cuda.matmul.allow_tf32 = True
             try:
-                dw0 = _tn_matmul(dz0, rows)
+                dw0 = tn_matmul(dz0, rows)
                 db0 = dz0.sum(dim=0)
-                dw1 = _tn_matmul(dz1, hidden) if two else None
+                dw1 = tn_matmul(dz1, hidden) if two else None
                 db1 = dz1.sum(dim=0) if two else None
                 dwh = (d_sdf[None, :] @ hidden)
                 dbh = d_sdf.sum().reshape(1)
             finally:
                 torch.backends.cuda.matmul.allow_tf32 = prev
         return dx, dw0, db0, dw1, db1, dwh, dbh, None, None, None
-
-
-def _tn_matmul(a, b):
-    """a^T b for tall operands a [M,p], b [M,q] (M >> p, q: a weight gradient, a reduction over all rows).  As one
-    GEMM the output has only a handful of tiles and the library runs it on a few SMs (measured 312 us for
-    M = 262144, p = 256, q = 131); split along M into independent batched products it fills the GPU."""
-    m = a.shape[0]
-    for parts in (64, 32, 16, 8):
-        if m % parts == 0 and m // parts >= 1024:
-            return torch.bmm(a.view(parts, m // parts, a.shape[1]).transpose(1, 2),
-                             b.reshape(parts, m // parts, b.shape[1])).sum(dim=0)
-    return a.t() @ b
 
 
 def fused_sdf_mlp(mlp, rows, beta, with_sdf=True, with_feat=True, packed=None):

@@ -31,6 +31,45 @@ def get_activation(activ, **kwargs):
     raise KeyError(activ)
 
 
+def tn_matmul(a, b):
+    """a^T b for tall operands a [M,p], b [M,q] (M >> p, q: a weight gradient, i.e. a reduction over all rows).  As one
+    GEMM the output has only a handful of tiles and the library runs it on a few SMs (measured on B200: 312 us for
+    M = 262144, p = 256, q = 131); split along M into independent batched products it fills the GPU."""
+    m = a.shape[0]
+    for parts in (64, 32, 16, 8):
+        if m % parts == 0 and m // parts >= 1024:
+            return torch.bmm(a.reshape(parts, m // parts, a.shape[1]).transpose(1, 2),
+                             b.reshape(parts, m // parts, b.shape[1])).sum(dim=0)
+    return a.t() @ b
+
+
+class _LinearTallRows(torch.autograd.Function):
+    """y = x W^T + b with the weight gradient evaluated by `tn_matmul` (the forward and dx are the library GEMMs
+    F.linear would run; only dW, a [out,in] result reduced over >= 8192 rows, is re-shaped into a split-K batch)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        ctx.save_for_backward(x, w)
+        return torch.addmm(b, x, w.t())
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy = dy.contiguous()
+        dx = dy @ w if ctx.needs_input_grad[0] else None
+        dw = tn_matmul(dy, x) if ctx.needs_input_grad[1] else None
+        db = dy.sum(dim=0) if ctx.needs_input_grad[2] else None
+        return dx, dw, db
+
+
+def linear(x, w, b):
+    """F.linear; on CUDA with many rows and a graph to build, the variant whose weight gradient is split-K."""
+    if x.is_cuda and x.dim() == 2 and x.shape[0] >= 8192 and b is not None and torch.is_grad_enabled() and \
+            (w.requires_grad or x.requires_grad):
+        return _LinearTallRows.apply(x, w, b)
+    return F.linear(x, w, b)
+
+
 class Linear(torch.nn.Module):
     """nn.Linear, optionally weight-normed with the legacy `weight_g` / `weight_v` parameter names of
     `torch.nn.utils.weight_norm` (dim=0: one norm per output row)."""
@@ -63,7 +102,10 @@ class Linear(torch.nn.Module):
         return self.weight_v * (self.weight_g / self.weight_v.norm(dim=1, keepdim=True))
 
     def forward(self, x):
-        return F.linear(x, self.effective_weight(), self.bias)
+        if x.dim() > 2 and x.is_cuda:
+            lead = x.shape[:-1]
+            return linear(x.reshape(-1, x.shape[-1]), self.effective_weight(), self.bias).view(*lead, -1)
+        return linear(x, self.effective_weight(), self.bias)
 
 
 class MLPforNeuralSDF(torch.nn.Module):
