@@ -9,7 +9,7 @@ import torch
 
 from . import _lib
 from ._lib import ptr
-from .mlp import tn_matmul
+from .mlp import colsum, tn_matmul
 
 _L = _lib.lib
 LO_SCALE = 2048.0
@@ -177,15 +177,15 @@ class FusedSdfMlpFunction(torch.autograd.Function):
                 w1t_hi, w1t_lo = (packed.w1t_hi, packed.w1t_lo) if packed is not None else \
                     pack_weight(w1.detach().float().t().contiguous(), n)
                 bound = d_feat.abs().amax(dim=1).contiguous()
-                colsum = w1.detach().abs().sum(dim=0).max().reshape(1) if packed is None else None
+                w1_colsum = w1.detach().abs().sum(dim=0).max().reshape(1) if packed is None else None
                 dz1 = torch.empty(m, n, dtype=torch.float32, device=dev)
             else:
                 w1t_hi = w1t_lo = bound = dz1 = None
-                colsum = torch.zeros(1, device=dev) if packed is None else None
+                w1_colsum = torch.zeros(1, device=dev) if packed is None else None
             if packed is not None:   # the two-layer bound is also valid (merely looser) for SDF-only rows
                 norms = packed.norms
             else:
-                norms = torch.cat([colsum.float(), w_head.abs().max().reshape(1)])   # device scalars: no host sync
+                norms = torch.cat([w1_colsum.float(), w_head.abs().max().reshape(1)])   # device scalars: no host sync
             dz0 = torch.empty(m, n, dtype=torch.float32, device=dev)
             dx = torch.empty(m, k0, dtype=torch.float32, device=dev)
             rc = _L().na_sdf_mlp_bwd(m, n, k0, k0_pad, 1 if two else 0, ptr(d_sdf), ptr(d_feat) if two else None,
@@ -199,9 +199,9 @@ class FusedSdfMlpFunction(torch.autograd.Function):
             torch.backends.cuda.matmul.allow_tf32 = True
             try:
                 dw0 = tn_matmul(dz0, rows)
-                db0 = dz0.sum(dim=0)
+                db0 = colsum(dz0)
                 dw1 = tn_matmul(dz1, hidden) if two else None
-                db1 = dz1.sum(dim=0) if two else None
+                db1 = colsum(dz1) if two else None
                 dwh = (d_sdf[None, :] @ hidden)
                 dbh = d_sdf.sum().reshape(1)
             finally:

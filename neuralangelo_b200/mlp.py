@@ -43,6 +43,16 @@ def tn_matmul(a, b):
     return a.t() @ b
 
 
+def colsum(a):
+    """a.sum(dim=0) of a tall contiguous [M,p] matrix (a bias gradient).  ATen's reduction over the slow dimension
+    runs at a quarter of the HBM bandwidth for M >= 65536 (measured on B200: 168 us for 262144 x 256 fp32); summing 64
+    row blocks first and the 64 partial rows afterwards takes 65 us (and rounds less)."""
+    m = a.shape[0]
+    if a.is_contiguous() and m % 64 == 0 and m >= 4096:
+        return a.view(64, m // 64, a.shape[1]).sum(dim=1).sum(dim=0)
+    return a.sum(dim=0)
+
+
 class _LinearTallRows(torch.autograd.Function):
     """y = x W^T + b with the weight gradient evaluated by `tn_matmul` (the forward and dx are the library GEMMs
     F.linear would run; only dW, a [out,in] result reduced over >= 8192 rows, is re-shaped into a split-K batch)."""
@@ -58,7 +68,7 @@ class _LinearTallRows(torch.autograd.Function):
         dy = dy.contiguous()
         dx = dy @ w if ctx.needs_input_grad[0] else None
         dw = tn_matmul(dy, x) if ctx.needs_input_grad[1] else None
-        db = dy.sum(dim=0) if ctx.needs_input_grad[2] else None
+        db = colsum(dy) if ctx.needs_input_grad[2] else None
         return dx, dw, db
 
 
