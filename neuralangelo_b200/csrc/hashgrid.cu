@@ -164,7 +164,6 @@ template <int F>
 struct Shape {
     static constexpr int V = F >= 4 ? 4 : 2;
     static constexpr int LPP = F / V;            // lanes per point
-    static constexpr int PTS = kThreads / LPP;   // points per CTA
 };
 
 // ---------------------------------------------------------------------------------------------

@@ -13,14 +13,15 @@
 // result = D_main + 2^-11 D_cross (the dropped a_lo b_lo term is 2^-22 relative) -- fp32-grade products at
 // 1.5x the cost of one TF32 pass.
 //
-// Structure (one CTA per SM, persistent over 128-row tiles; M = 128, N = H <= 256, cta_group::1):
-//   warps 0-7  compute: stage the input tile into shared memory as fp16 hi/lo in the UMMA core-matrix order,
-//              then per layer read the accumulators back (tcgen05.ld), add bias, softplus, take the SDF head's
-//              dot product on the fly, and write the activations straight back to shared memory as the next
-//              layer's A operand -- intermediate activations never touch HBM;
-//   warp 8     MMA issuer (one elected lane issues tcgen05.mma, tcgen05.commit signals mbarriers);
-//   warp 9     weight loader: cp.async.bulk (TMA, 1-D) streams pre-packed 16-wide K blocks of W_hi / W_lo
-//              through a 5-stage ring, running ahead across layers and tiles.
+// Two forward kernels (one CTA per SM, persistent over 128-row tiles; M = 128, cta_group::1):
+//  * sdf_mlp_fwd_kernel -- both layers (SDF + feature).  Sixteen compute warps (four column groups x four TMEM lane
+//    quarters) stage the input tile into shared memory as fp16 hi/lo in the UMMA core-matrix order, then per layer read
+//    the accumulators back (tcgen05.ld), add bias, softplus, take the SDF head's dot product on the fly, and write the
+//    activations straight back to shared memory as the next layer's A operand -- intermediate activations never touch
+//    HBM; one MMA warp (an elected lane issues tcgen05.mma, tcgen05.commit signals mbarriers); one loader warp
+//    streams pre-packed 16-wide K blocks of W_hi / W_lo through a 5-stage cp.async.bulk ring, running ahead across
+//    layers and tiles.
+//  * sdf_head_fwd_pipe_kernel -- the SDF-only evaluation (first layer + head), pipelined: see its own header below.
 // Operands are K-major without swizzle: element (row, k) of a tile with R rows sits at
 //     (k / 8) * (R / 8 * 128) + (row / 8) * 128 + (row % 8) * 16 + (k % 8) * 2   bytes,
 // so a thread that owns one row writes its eight-column chunks with conflict-free 16-byte stores and the
@@ -192,7 +193,6 @@ __global__ void __launch_bounds__(kFwdThreads, 1) sdf_mlp_fwd_kernel(const __gri
         }
     } else {
         // ===================== compute warps =====================
-        const int tid = threadIdx.x;                // 0..255
         const int quarter = warp & 3;               // TMEM lane quarter this warp may access
         const int group = warp >> 2;                // which slice of the N columns this warp handles
         const int cols_per_group = n / kFwdGroups >= 32 ? n / kFwdGroups : 32;
@@ -353,7 +353,6 @@ constexpr int kPipeWarps = 16;
 constexpr int kPipeCompute = kPipeWarps * 32;
 constexpr int kPipeThreads = kPipeCompute + 32;   // + MMA warp (also loads the weights once)
 constexpr int kPipeBars = 8;
-constexpr int kPipeRounds = 8;                    // up to 8 x 32 input columns
 constexpr int kPipeTail = 4;                      // + up to 4 more
 
 __host__ __device__ inline uint32_t pipe_smem_bytes(int k_pad, int n) {
