@@ -236,6 +236,15 @@ int na_adamw_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq
  * (zero gradient, zero moments: AdamW reduces to p *= 1 - lr*wd per step) when they become active. */
 int na_scale_inplace(float* params, int64_t n, float factor, void* stream);
 
+/* Weight-norm reparametrisation of one layer, w[r,:] = g[r] * v[r,:] / ||v[r,:]|| (fp32, row-major [rows, cols]), and
+ * its adjoint: dg[r] = <dw[r], v[r]> / ||v[r]||, dv[r] = (g[r] / ||v[r]||) (dw[r] - v[r] dg[r] / ||v[r]||).
+ * inv_norm [rows] is written by the forward and read by the backward.  One launch each.
+ * Replaces: torch.nn.utils.weight_norm on every MLP layer, projects/neuralangelo/utils/mlp.py:37-38 and
+ *   projects/nerf/utils/nerf_util.py:176-177 (three ATen kernels per layer forward, about six backward). */
+int na_weight_norm_fwd(const float* v, const float* g, int rows, int cols, float* w, float* inv_norm, void* stream);
+int na_weight_norm_bwd(const float* v, const float* g, const float* inv_norm, const float* dw, int rows, int cols,
+                       float* dv, float* dg, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Fused SDF MLP forward on tcgen05 tensor cores (accumulators in TMEM, activations stay on chip):
  *   h0 = softplus_beta(x W0^T + b0);  sdf = h0 . w_head + b_head;  [feat = softplus_beta(h0 W1^T + b1)]

@@ -80,6 +80,35 @@ def linear(x, w, b):
     return F.linear(x, w, b)
 
 
+class _WeightNorm(torch.autograd.Function):
+    """W = g * v / ||v|| per output row as ONE launch forward and one backward (csrc/weight_norm.cu) instead of the
+    ~nine ATen kernels of the composite expression; used on CUDA only (the CPU path keeps the torch expression)."""
+
+    @staticmethod
+    def forward(ctx, v, g):
+        from . import _lib
+        vc, gc = v.detach().contiguous(), g.detach().reshape(-1).contiguous()
+        rows, cols = vc.shape
+        w = torch.empty_like(vc)
+        inv = torch.empty(rows, dtype=torch.float32, device=vc.device)
+        _lib.check(_lib.lib().na_weight_norm_fwd(_lib.ptr(vc), _lib.ptr(gc), rows, cols, _lib.ptr(w), _lib.ptr(inv),
+                                                 _lib.current_stream()), "na_weight_norm_fwd")
+        ctx.save_for_backward(vc, gc, inv)
+        ctx.g_shape = g.shape
+        return w
+
+    @staticmethod
+    def backward(ctx, dw):
+        from . import _lib
+        vc, gc, inv = ctx.saved_tensors
+        rows, cols = vc.shape
+        dwc = dw.contiguous()
+        dv, dg = torch.empty_like(vc), torch.empty_like(gc)
+        _lib.check(_lib.lib().na_weight_norm_bwd(_lib.ptr(vc), _lib.ptr(gc), _lib.ptr(inv), _lib.ptr(dwc), rows, cols,
+                                                 _lib.ptr(dv), _lib.ptr(dg), _lib.current_stream()), "na_weight_norm_bwd")
+        return dv, dg.view(ctx.g_shape)
+
+
 class Linear(torch.nn.Module):
     """nn.Linear, optionally weight-normed with the legacy `weight_g` / `weight_v` parameter names of
     `torch.nn.utils.weight_norm` (dim=0: one norm per output row)."""
@@ -109,6 +138,8 @@ class Linear(torch.nn.Module):
     def effective_weight(self):
         if not self.weight_norm:
             return self.weight
+        if self.weight_v.is_cuda and self.weight_v.dtype == torch.float32:
+            return _WeightNorm.apply(self.weight_v, self.weight_g)
         return self.weight_v * (self.weight_g / self.weight_v.norm(dim=1, keepdim=True))
 
     def forward(self, x):

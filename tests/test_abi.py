@@ -18,7 +18,7 @@ def test_header_declares_the_expected_surface():
     for must in ("na_hashgrid_fwd", "na_hashgrid_bwd", "na_hashgrid_taps_fwd", "na_hashgrid_taps_bwd", "na_sdf_mlp_fwd", "na_sdf_head_fwd_planes",
                  "na_sdf_mlp_bwd", "na_mlp_chain_fwd", "na_neus_render_fwd", "na_neus_render_bwd", "na_alpha_weights_fwd",
                  "na_sample_pdf", "na_neus_upsample", "na_merge_sorted", "na_mc_count", "na_mc_emit", "na_adamw_step",
-                 "na_last_error", "na_abi_version"):
+                 "na_weight_norm_fwd", "na_weight_norm_bwd", "na_last_error", "na_abi_version"):
         assert must in names, must
 
 

@@ -227,3 +227,23 @@ def test_fused_chain_background_nerf(na_lib, cuda_device):
         rgb, dens = fused_chain.background_forward(bg, enc, venc)
     assert (rgb.cpu().double() - ref_rgb).abs().max().item() <= 5e-6
     assert (dens.cpu().double() - ref_dens).abs().max().item() <= 5e-6 * max(ref_dens.abs().max().item(), 1.0)
+
+
+@pytest.mark.parametrize("rows,cols", [(256, 278), (257, 84), (3, 256), (1, 256), (64, 131)])
+def test_fused_weight_norm_forward_and_backward(na_lib, cuda_device, rows, cols):
+    """csrc/weight_norm.cu against the torch expression of torch.nn.utils.weight_norm (dim=0) in float64."""
+    from neuralangelo_b200.mlp import _WeightNorm
+    g0 = torch.Generator().manual_seed(rows * 1000 + cols)
+    v = torch.randn(rows, cols, generator=g0) * 0.3
+    g = torch.rand(rows, 1, generator=g0) + 0.5
+    dw = torch.randn(rows, cols, generator=g0)
+    vd, gd = v.double().requires_grad_(True), g.double().requires_grad_(True)
+    wd = vd * (gd / vd.norm(dim=1, keepdim=True))
+    wd.backward(dw.double())
+    vk, gk = v.to(cuda_device).requires_grad_(True), g.to(cuda_device).requires_grad_(True)
+    wk = _WeightNorm.apply(vk, gk)
+    wk.backward(dw.to(cuda_device))
+    torch.testing.assert_close(wk.detach().cpu().double(), wd.detach(), rtol=2e-6, atol=1e-7)
+    torch.testing.assert_close(vk.grad.cpu().double(), vd.grad, rtol=2e-5, atol=2e-6)
+    torch.testing.assert_close(gk.grad.cpu().double(), gd.grad, rtol=2e-5, atol=2e-6)
+    assert gk.grad.shape == (rows, 1)
