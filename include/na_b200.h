@@ -7,9 +7,7 @@
  *   - return 0 on success, a negative NA_ERR_* code otherwise; the message is
  *     retrievable (thread-local) with na_last_error().  Nothing throws or aborts.
  *   - `stream` is a cudaStream_t passed as void*.  Calls are asynchronous on that
- *     stream: no implicit device synchronisation, no allocation (the *_host
- *     convenience entry points, which take HOST buffers, are the documented
- *     exception: they allocate, copy, run and synchronise).
+ *     stream: no implicit device synchronisation, no allocation.
  *   - the caller has made the right device current (cudaSetDevice) beforehand.
  *
  * "Replaces" cites the reference interface (path:line under the reference tree)

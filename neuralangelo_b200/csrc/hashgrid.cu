@@ -406,6 +406,24 @@ hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
 // one 128 MiB hashed level is the working set).  Measured on B200, 2^22 random points, default
 // table (profiles/r01_hashgrid_mapping_sweep.md): 1 level/pass is best for a single evaluation,
 // 2 levels/pass for the 7-evaluation tap kernel whose traffic is dominated by feature rows.
+// Developer knobs of the sweep above.  Compiled in only with -DNA_HG_DEV_KNOBS (scripts/microbench_hashgrid.py
+// documents the build); read once, clamped to valid values.  The shipped library uses the measured defaults.
+struct DevKnobs {
+    int group = 0;   // 0 = default mapping
+    int iters = 16;  // points per warp and CTA
+};
+const DevKnobs& dev_knobs() {
+    static const DevKnobs k = [] {
+        DevKnobs v;
+#ifdef NA_HG_DEV_KNOBS
+        if (const char* e = getenv("NA_HG_GROUP")) v.group = atoi(e) > 0 ? atoi(e) : 0;
+        if (const char* e = getenv("NA_HG_ITERS")) v.iters = atoi(e) >= 1 ? (atoi(e) > 4096 ? 4096 : atoi(e)) : 16;
+#endif
+        return v;
+    }();
+    return k;
+}
+
 Mapping make_mapping(const na_hashgrid_desc* desc, uint32_t levels, uint32_t n_taps, bool planes) {
     Mapping m;
     m.lanes_per_level = desc->n_features >= 4 ? desc->n_features / 4 : 1;
@@ -413,14 +431,14 @@ Mapping make_mapping(const na_hashgrid_desc* desc, uint32_t levels, uint32_t n_t
     // level-major feature planes: consecutive points are consecutive in memory, so one level per pass is both
     // the coalesced and the L2-friendly choice
     int cap = (n_taps > 1 && !planes) ? 2 : 1;
-    if (const char* e = getenv("NA_HG_GROUP")) cap = atoi(e);  // developer knob for the sweep above
+    if (dev_knobs().group > 0) cap = dev_knobs().group;
     if (cap > max_levels_per_warp) cap = max_levels_per_warp;
     int lp = 1;  // levels per pass: power of two so that points-per-warp divides the warp
     while (lp < (int)levels && lp < cap) lp *= 2;
     m.levels_per_pass = lp;
     m.points_per_warp = 32 / (lp * m.lanes_per_level);
     m.passes = ((int)levels + lp - 1) / lp;
-    m.points_per_cta = 8 * m.points_per_warp * (getenv("NA_HG_ITERS") ? atoi(getenv("NA_HG_ITERS")) : 16);
+    m.points_per_cta = 8 * m.points_per_warp * dev_knobs().iters;
     return m;
 }
 

@@ -193,19 +193,14 @@ class FusedSdfMlpFunction(torch.autograd.Function):
                                      ptr(w0t_hi), ptr(w0t_lo), ptr(w_head), ctx.beta, ptr(norms), ptr(dz1), ptr(dz0),
                                      ptr(dx), k0, _lib.current_stream())
             _lib.check(rc, "na_sdf_mlp_bwd")
-            # weight gradients: reductions over the rows (TF32 is what the reference itself runs its GEMMs in,
-            # imaginaire/trainers/base.py:172-175)
-            prev = torch.backends.cuda.matmul.allow_tf32
-            torch.backends.cuda.matmul.allow_tf32 = True
-            try:
-                dw0 = tn_matmul(dz0, rows)
-                db0 = colsum(dz0)
-                dw1 = tn_matmul(dz1, hidden) if two else None
-                db1 = colsum(dz1) if two else None
-                dwh = (d_sdf[None, :] @ hidden)
-                dbh = d_sdf.sum().reshape(1)
-            finally:
-                torch.backends.cuda.matmul.allow_tf32 = prev
+            # weight gradients: reductions over the rows, in the ambient matmul precision (TrainStep enables TF32 by
+            # default, as the reference's trainer does: imaginaire/trainers/base.py:172-175)
+            dw0 = tn_matmul(dz0, rows)
+            db0 = colsum(dz0)
+            dw1 = tn_matmul(dz1, hidden) if two else None
+            db1 = colsum(dz1) if two else None
+            dwh = (d_sdf[None, :] @ hidden)
+            dbh = d_sdf.sum().reshape(1)
         return dx, dw0, db0, dw1, db1, dwh, dbh, None, None, None
 
 

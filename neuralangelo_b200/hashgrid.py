@@ -153,6 +153,9 @@ class _HashGridTaps(torch.autograd.Function):
         (x,) = ctx.saved_tensors
         module = ctx.module
         unit_map, active_levels, tap_offsets = ctx.args
+        if ctx.needs_input_grad[0]:
+            raise NotImplementedError("hash-grid encode: the gradient w.r.t. the query points is not implemented "
+                                      "(numerical-gradient mode never needs it) -- detach the points")
         if not ctx.needs_input_grad[1]:
             return None, None, None, None, None, None
         dtable = module._grad_buffer()

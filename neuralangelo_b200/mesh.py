@@ -86,7 +86,7 @@ class Mesh:
         self.faces = self.faces[np.asarray(mask)]
 
     def split(self, only_watertight=False):
-        """Connected components (by shared vertices) as separate meshes."""
+        """Connected components of the face-adjacency graph (shared edges, as trimesh) as separate meshes."""
         labels = _face_components(self.faces, len(self.vertices))
         out = []
         for lab in np.unique(labels):
@@ -116,29 +116,21 @@ class Mesh:
 
 
 def _face_components(faces, n_vertices):
-    """Union-find over vertices; returns the component label of each face."""
-    parent = np.arange(n_vertices, dtype=np.int64)
-
-    def find(x):
-        while True:
-            p = parent[x]
-            gp = parent[p]
-            if np.array_equal(p, gp):
-                return p
-            parent[x] = gp
-            x = gp
-
-    if len(faces) == 0:
+    """Component label of each face, faces being connected when they SHARE AN EDGE -- the face-adjacency graph
+    trimesh.Trimesh.split walks (reference mesh.py:152); two pieces touching in a single vertex stay separate."""
+    from scipy.sparse import coo_matrix
+    from scipy.sparse.csgraph import connected_components
+    n_f = len(faces)
+    if n_f == 0:
         return np.zeros(0, dtype=np.int64)
-    for a, b in ((0, 1), (1, 2)):
-        while True:
-            ra, rb = find(faces[:, a]), find(faces[:, b])
-            diff = ra != rb
-            if not diff.any():
-                break
-            lo, hi = np.minimum(ra[diff], rb[diff]), np.maximum(ra[diff], rb[diff])
-            parent[hi] = lo
-    return find(faces[:, 0])
+    f = np.asarray(faces, dtype=np.int64)
+    edges = np.sort(np.concatenate([f[:, [0, 1]], f[:, [1, 2]], f[:, [2, 0]]]), axis=1)   # [3F,2], face = row % F
+    key = edges[:, 0] * np.int64(n_vertices) + edges[:, 1]
+    order = np.argsort(key, kind="stable")
+    same = key[order][1:] == key[order][:-1]          # consecutive occurrences of one edge: their faces are adjacent
+    fa, fb = order[:-1][same] % n_f, order[1:][same] % n_f
+    graph = coo_matrix((np.ones(len(fa), dtype=np.int8), (fa, fb)), shape=(n_f, n_f))
+    return connected_components(graph, directed=False)[1].astype(np.int64)
 
 
 def concatenate(meshes):

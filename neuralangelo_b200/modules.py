@@ -61,6 +61,9 @@ class _EncodeRows(torch.autograd.Function):
         (pts,) = ctx.saved_tensors
         module = ctx.module
         unit_map, active_levels, taps = ctx.args
+        if ctx.needs_input_grad[0]:
+            raise NotImplementedError("hash-grid encode: the gradient w.r.t. the query points (analytical normals, "
+                                      "pose optimisation; modules.py:117-130) is not implemented -- detach the points")
         if not ctx.needs_input_grad[1]:
             return None, None, None, None, None, None
         dtable = module._grad_buffer()
@@ -71,6 +74,9 @@ class _EncodeRows(torch.autograd.Function):
 
 
 class NeuralSDF(torch.nn.Module):
+
+    # explicit opt-in: evaluate an MLP architecture the fused kernels do not cover with torch ops (never implicit)
+    allow_torch_mlp = False
 
     def __init__(self, cfg_sdf):
         super().__init__()
@@ -198,8 +204,16 @@ class NeuralSDF(torch.nn.Module):
     def run_mlp(self, rows, with_sdf=True, with_feat=True):
         """rows [...,3+LD] -> [sdf [...,1] | None, feat [...,K] | None]."""
         needs_graph = torch.is_grad_enabled() and (rows.requires_grad or any(p.requires_grad for p in self.mlp.parameters()))
-        packed = self._packed_mlp() if rows.is_cuda else None
+        _lib.require_cuda(rows)
+        packed = self._packed_mlp()
         if packed is None:
+            # outside the tcgen05 kernels' envelope (softplus, one hidden layer, no skip, width 64..256, input <= 256):
+            # there is no silent fallback -- torch ops run only when the caller has opted in explicitly
+            if not self.allow_torch_mlp:
+                raise NotImplementedError(
+                    "NeuralSDF MLP is outside the fused kernel's envelope (softplus, num_layers=1, no skip connection, "
+                    "hidden width 64/128/192/256, input width <= 256); set NeuralSDF.allow_torch_mlp = True to "
+                    "evaluate it with torch ops")
             return self.mlp(rows, with_sdf=with_sdf, with_feat=with_feat)
         flat = rows.reshape(-1, rows.shape[-1])
         if flat.stride(-1) != 1 or flat.dtype != torch.float32:

@@ -187,23 +187,32 @@ class _NeusRender(torch.autograd.Function):
                                            _lib.current_stream()), "na_neus_render_fwd")
         ctx.save_for_backward(sdf, grad, s_var, rgb_obj, dens_bg, rgb_bg, dists_obj, ray_unit, dist_far, dists_bg)
         ctx.anneal_ratio = anneal_ratio
-        ctx.mark_non_differentiable(opacity)
+        # opacity = sum of the weights is differentiable (model.py:138-140 adds 1 - opacity_all to the colour for a
+        # white background); unused outputs arrive as None in backward instead of materialised zeros
+        ctx.set_materialize_grads(False)
         if weights is None:
             weights = torch.empty(0, device=sdf.device)
             ctx.mark_non_differentiable(weights)
         return rgb, weights, opacity
 
     @staticmethod
-    def backward(ctx, d_rgb, d_weights, _d_opacity):
+    def backward(ctx, d_rgb, d_weights, d_opacity):
         sdf, grad, s_var, rgb_obj, dens_bg, rgb_bg, dists_obj, ray_unit, dist_far, dists_bg = ctx.saved_tensors
         n_obj = sdf.shape[-1]
         n_bg = 0 if dens_bg is None else dens_bg.shape[-1]
         rays = sdf.numel() // n_obj
+        if d_rgb is None:
+            d_rgb = torch.zeros(*sdf.shape[:-1], 3, dtype=torch.float32, device=sdf.device)
         d_sdf, d_grad, d_rgb_obj = torch.empty_like(sdf), torch.empty_like(grad), torch.empty_like(rgb_obj)
         d_s = torch.zeros_like(s_var)
         d_dens = torch.empty_like(dens_bg) if n_bg else None
         d_rgb_bg = torch.empty_like(rgb_bg) if n_bg else None
         dw = f32c(d_weights) if (d_weights is not None and d_weights.numel() == rays * (n_obj + n_bg)) else None
+        if d_opacity is not None:   # opacity = sum_i w_i  =>  every weight receives d_opacity of its ray
+            d_op = f32c(d_opacity).reshape(*sdf.shape[:-1], 1)
+            dw = (dw.reshape(*sdf.shape[:-1], n_obj + n_bg) + d_op) if dw is not None else \
+                d_op.expand(*sdf.shape[:-1], n_obj + n_bg)
+            dw = dw.contiguous()
         _lib.check(_L().na_neus_render_bwd(ptr(sdf), ptr(grad), ptr(dists_obj), ptr(ray_unit), ptr(dist_far), ptr(s_var),
                                            ptr(ctx.anneal_ratio), ptr(rgb_obj), n_obj, ptr(dens_bg), ptr(dists_bg),
                                            ptr(rgb_bg), n_bg, rays, ptr(f32c(d_rgb)), ptr(dw), ptr(d_sdf), ptr(d_grad),

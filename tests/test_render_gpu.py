@@ -113,6 +113,39 @@ def test_fused_render_vs_oracle(na_lib, cuda_device, R, N, NB):
     assert abs(sk.grad.item() - so.grad.item()) <= 2e-4 * abs(so.grad.item()) + 1e-6
 
 
+@pytest.mark.parametrize("want_weights", [True, False])
+def test_white_background_gradient_through_opacity(na_lib, cuda_device, want_weights):
+    """model.py:138-140 with background.white: rgb + (1 - opacity_all) back-propagates through the opacity
+    (= sum of the compositing weights).  Oracle: float64 autograd of oracle/render_ref.py."""
+    from neuralangelo_b200 import render
+    R, N, NB = 97, 64, 16
+    ray, dists, sdf, grad, far, rgb, dens, dbg, rgbb, tgt = _scene(R, N, NB, seed=11)
+    s = torch.tensor(2.5)
+    leaf = lambda t: t.clone().requires_grad_(True)
+    o_in = [leaf(t.double()) for t in (sdf, grad, rgb, dens, rgbb)]
+    so = s.double().requires_grad_(True)
+    o_rgb, o_w, o_op = rr.neus_render(o_in[0], o_in[1], dists.double(), ray.double(), far.double(), so, 0.3, o_in[2],
+                                      dens_bg=o_in[3], dists_bg=dbg.double(), rgb_bg=o_in[4])
+    o_white = o_rgb + (1 - o_op[..., None])
+    ((o_white - tgt.double()) ** 2).sum().backward()
+    d = cuda_device
+    k_in = [leaf(t.to(d)) for t in (sdf, grad, rgb, dens, rgbb)]
+    sk = s.to(d).requires_grad_(True)
+    B = lambda t: t[None]
+    k_rgb, k_w, k_op = render.neus_render(B(ray.to(d)), B(k_in[0])[..., None], B(k_in[1]), B(dists.to(d))[..., None], sk,
+                                          B(k_in[2]), dist_far=B(far.to(d))[..., None, None], progress=0.03, anneal_end=0.1,
+                                          densities_bg=B(k_in[3]), dists_bg=B(dbg.to(d))[..., None], rgbs_bg=B(k_in[4]),
+                                          want_weights=want_weights)
+    k_white = k_rgb + (1 - k_op)
+    torch.testing.assert_close(k_white[0].cpu().double(), o_white.detach(), rtol=2e-5, atol=2e-6)
+    ((k_white[0] - tgt.to(d)) ** 2).sum().backward()
+    for name, ko, oo in zip(["sdf", "grad", "rgb_obj", "dens_bg", "rgb_bg"], k_in, o_in):
+        scale = oo.grad.abs().max().item() + 1e-12
+        err = (ko.grad.cpu().double() - oo.grad).abs().max().item()
+        assert err <= 2e-4 * scale + 1e-7, (name, err, scale)
+    assert abs(sk.grad.item() - so.grad.item()) <= 2e-4 * abs(so.grad.item()) + 1e-6
+
+
 def test_alpha_weights_backward_with_saturated_alphas(na_lib, cuda_device):
     """alpha == 1 exactly (reachable through the clip at model.py:290): ATen's cumprod backward needs a
     special path here; the reverse affine scan must simply give the analytic gradient."""
