@@ -187,6 +187,169 @@ def model_fixtures():
               "table grad nnz", int((model.neural_sdf.tcnn_encoding.params.grad != 0).sum()))
 
 
+def _look_at(eye):
+    eye = torch.tensor(eye, dtype=torch.float32)
+    fwd = -eye / eye.norm()
+    right = torch.linalg.cross(torch.tensor([0.0, 1.0, 0.0]), fwd)
+    right = right / right.norm()
+    up = torch.linalg.cross(fwd, right)
+    R = torch.stack([right, up, fwd], dim=0)    # world -> camera rotation
+    return torch.cat([R, (-R @ eye)[:, None]], dim=1)
+
+
+DEFAULT_CASES = ((4, 16), (6, 16), (4, 9))   # (taps, active levels) of the default-config fixtures
+
+
+def default_model_fixtures(cases=DEFAULT_CASES, n_rays=16):
+    """The UNMODIFIED reference model at base.yaml's DEFAULT shape (16 levels x 8 features, dict_size 22, 256-wide
+    MLPs, 64 + 4 x 16 object and 32 background samples) on the CPU, hash grid by oracle/tcnn_stub.py: train-mode
+    render_rays + loss + backward.  Too large to store whole -- see oracle/golden_recipe.py: the table and the large
+    weight tensors are recorded as recipes; the table gradient as per-level checksums plus a sample of entries; large
+    MLP gradients as norm + a sample."""
+    from . import tcnn_stub, golden_recipe as gr
+    reference_shim.install(tcnn_module=tcnn_stub)
+    from neuralangelo_b200.config import AttrDict, default_model_config
+    from projects.neuralangelo.model import Model
+    from projects.neuralangelo.utils.misc import eikonal_loss, curvature_loss
+
+    for taps, active in cases:
+        torch.manual_seed(4321 + taps)
+        cfg_model = default_model_config()
+        cfg_model.object.sdf.gradient.taps = taps
+        cfg_model.render.rand_rays = n_rays
+        cfg_model.render.stratified = False
+        cfg_data = AttrDict(num_images=None, train=dict(image_size=[40, 48]), val=dict(image_size=[10, 12]))
+        model = Model(cfg_model, cfg_data)
+        fx = {}
+        # ---- parameters: big tensors from recipes (same statistics as the reference's own initialisation) ----
+        table_seed, table_amp = 777 + taps, 0.05
+        enc = model.neural_sdf.tcnn_encoding
+        with torch.no_grad():
+            enc.params.copy_(torch.from_numpy(gr.table_tensor(table_seed, enc.params.numel(), table_amp)))
+            seed = 1000 * taps + active
+            for name, p in sorted(model.named_parameters()):
+                if p is enc.params or p.numel() < gr.BIG:
+                    continue
+                seed += 1
+                mean, std = float(p.mean()), float(p.std())
+                if name == "neural_sdf.mlp.linears.0.weight_v":
+                    # geometric init zeroes the encoding columns; give them weight so that the hash grid matters
+                    w = gr.normal_tensor(seed, p.shape, 0.0, 1.0)
+                    xyz_std = float(p[:, :3].std())
+                    w[:, :3] *= xyz_std
+                    w[:, 3:] *= 0.02
+                    p.copy_(torch.from_numpy(w))
+                    fx["recipe_" + name] = np.array([seed, -1.0, xyz_std, 0.02], dtype=np.float64)
+                else:
+                    p.copy_(torch.from_numpy(gr.normal_tensor(seed, p.shape, mean, std)))
+                    fx["recipe_" + name] = np.array([seed, mean, std, 0.0], dtype=np.float64)
+        fx["table_recipe"] = np.array([table_seed, table_amp, enc.params.numel()], dtype=np.float64)
+        for k, v in model.state_dict().items():
+            if v.numel() < gr.BIG:
+                fx["sd_" + k] = _np(v)
+        model.train()
+        sdf = model.neural_sdf
+        sdf.warm_up_end = 5000
+        it = 5000 + active * 5000            # anneal = active (modules.py:97-100)
+        sdf.set_active_levels(it)
+        sdf.set_normal_epsilon()
+        assert sdf.active_levels == active
+        model.progress = 0.04
+        pose = torch.stack([_look_at([0.3, 0.2, -3.0])])
+        intr = torch.tensor([[70.0, 0.0, 24.0], [0.0, 70.0, 20.0], [0.0, 0.0, 1.0]]).repeat(1, 1, 1)
+        g = torch.Generator().manual_seed(99 + taps)
+        ray_idx = torch.stack([torch.randperm(40 * 48, generator=g)[:n_rays]])
+        target = torch.rand(1, n_rays, 3, generator=g)
+        out = model(dict(pose=pose, intr=intr, idx=torch.arange(1), ray_idx=ray_idx))
+        loss = 3 * torch.nn.functional.l1_loss(out["rgb"], target) + 0.1 * eikonal_loss(out["gradients"], out["outside"]) \
+            + 5e-4 * curvature_loss(out["hessians"], out["outside"])
+        loss.backward()
+        fx.update({"in_pose": _np(pose), "in_intr": _np(intr), "in_ray_idx": _np(ray_idx), "in_target": _np(target),
+                   "loss": _np(loss), "normal_eps": np.float64(sdf.normal_eps), "active_levels": np.int64(active),
+                   "iteration": np.int64(it), "taps": np.int64(taps)})
+        for k in ("rgb", "dists", "weights", "gradients", "hessians", "outside"):
+            fx["out_" + k] = _np(out[k])
+        # ---- gradients ----
+        for name, p in model.named_parameters():
+            if p is enc.params:
+                continue
+            gflat = p.grad.detach().flatten() if p.grad is not None else torch.zeros(0)
+            if p.numel() < gr.BIG:
+                fx["grad_" + name] = _np(gflat.view_as(p)) if p.grad is not None else np.zeros(0, dtype=np.float32)
+            else:
+                pos = gr.sample_positions(p.numel(), 4096, seed=17)
+                fx["gradnorm_" + name] = np.float64(gflat.double().norm())
+                fx["gradsample_" + name] = _np(gflat[torch.from_numpy(pos)])
+        tg = enc.params.grad.detach()
+        F = enc.tbl["n_features"]
+        lv_sum, lv_abs, lv_l2, lv_nnz = [], [], [], []
+        for lv in enc.tbl["levels"]:
+            part = tg[lv["offset"] * F:(lv["offset"] + lv["entries"]) * F].double()
+            lv_sum.append(float(part.sum())), lv_abs.append(float(part.abs().sum()))
+            lv_l2.append(float(part.norm())), lv_nnz.append(int((part != 0).sum()))
+        fx["tg_level_sum"], fx["tg_level_abs"] = np.array(lv_sum), np.array(lv_abs)
+        fx["tg_level_l2"], fx["tg_level_nnz"] = np.array(lv_l2), np.array(lv_nnz, dtype=np.int64)
+        nz = torch.nonzero(tg).flatten()
+        pick = nz[torch.from_numpy(gr.sample_positions(nz.numel(), 20000, seed=23))]
+        fx["tg_index"], fx["tg_value"] = _np(pick), _np(tg[pick])
+        # entries that must stay exactly zero (sample of untouched positions)
+        zpos = torch.from_numpy(gr.sample_positions(tg.numel(), 20000, seed=29))
+        zpos = zpos[tg[zpos] == 0]
+        fx["tg_zero_index"] = _np(zpos)
+        name = f"default_model_golden_taps{taps}_active{active}.npz"
+        np.savez_compressed(os.path.join(OUT, name), **fx)
+        print(f"wrote {name}: loss {float(loss):.6f}, outside rays {int(out['outside'].sum())}, table grad nnz "
+              f"{int(nz.numel())}, size {os.path.getsize(os.path.join(OUT, name)) / 1e3:.0f} kB")
+
+
+TEX_GAIN = 12.0   # factor on the colour head's weight_g for the texture fixture (applied on both sides)
+
+
+def inference_texture_fixtures():
+    """`Model.inference` (model.py:73-88: rgb / opacity / depth / normal maps of a validation view) and
+    `extract_texture` (utils/mesh.py:52-65) of the UNMODIFIED reference on the small golden models, weights taken from
+    model_golden_taps{4,6}.npz.  extract_texture hard-codes `.cuda()`; it is run with Tensor.cuda patched to the
+    identity, nothing else touched."""
+    from . import tcnn_stub
+    reference_shim.install(tcnn_module=tcnn_stub)
+    from neuralangelo_b200.config import AttrDict
+    from projects.neuralangelo.model import Model
+    from projects.neuralangelo.utils import mesh as ref_mesh
+    fx = {}
+    for taps in (4, 6):
+        z = np.load(os.path.join(OUT, f"model_golden_taps{taps}.npz"))
+        cfg_data = AttrDict(num_images=None, train=dict(image_size=[20, 24]), val=dict(image_size=[10, 12]))
+        model = Model(small_model_config(taps), cfg_data)
+        model.load_state_dict({k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd_")}, strict=True)
+        model.neural_sdf.warm_up_end = 5
+        model.neural_sdf.set_active_levels(35)
+        model.neural_sdf.set_normal_epsilon()
+        model.progress = 0.04
+        pose, intr = torch.from_numpy(z["in_pose"])[:1], torch.from_numpy(z["in_intr"])[:1]
+        intr_val = torch.tensor([[0.5, 0, 0], [0, 0.5, 0], [0, 0, 1.0]]) @ intr
+        out = model.inference(dict(pose=pose, intr=intr_val, idx=torch.arange(1)))
+        for k in ("rgb_map", "opacity_map", "depth_map", "normal_map"):
+            fx[f"inf{taps}_{k}"] = _np(out[k])
+        fx[f"inf{taps}_pose"], fx[f"inf{taps}_intr"] = _np(pose), _np(intr_val)
+        # texture: points near the model's zero level set (|x| ~ 0.5 after geometric init) and a few far from it
+        g = torch.Generator().manual_seed(50 + taps)
+        dirs = torch.nn.functional.normalize(torch.randn(160, 3, generator=g), dim=-1)
+        xyz = (dirs * (0.35 + 0.3 * torch.rand(160, 1, generator=g))).numpy().astype(np.float64)
+        with torch.no_grad():   # spread the colours: the random-init colour head outputs ~0.5 everywhere
+            model.neural_rgb.mlp.linears[-1].weight_g.mul_(TEX_GAIN)
+        orig_cuda = torch.Tensor.cuda
+        torch.Tensor.cuda = lambda self, *a, **k: self
+        try:
+            colors = ref_mesh.extract_texture(xyz, model.neural_rgb, model.neural_sdf, None)
+        finally:
+            torch.Tensor.cuda = orig_cuda
+        fx[f"tex{taps}_xyz"], fx[f"tex{taps}_colors"] = xyz, colors
+        print(f"taps {taps}: opacity range {float(out['opacity_map'].min()):.3f}..{float(out['opacity_map'].max()):.3f}, "
+              f"colour range {colors.min()}..{colors.max()}")
+    np.savez_compressed(os.path.join(OUT, "inference_texture_golden.npz"), **fx)
+    print("wrote inference_texture_golden.npz")
+
+
 def cpu_path_fixtures():
     """BASELINE.json configs[0] shape (Fourier-encoded NeuralSDF, no background, 6-tap gradients) on the UNMODIFIED
     reference model, 64-wide MLPs to keep the fixture small: state dict, rays, outputs, loss, parameter gradients."""
@@ -230,6 +393,11 @@ def cpu_path_fixtures():
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    render_fixtures()
-    model_fixtures()
-    cpu_path_fixtures()
+    import sys
+    if "--default-only" not in sys.argv:
+        render_fixtures()
+        model_fixtures()
+        cpu_path_fixtures()
+        inference_texture_fixtures()
+    if "--default" in sys.argv or "--default-only" in sys.argv:   # slow (1.46 GB table, dense autograd on the CPU)
+        default_model_fixtures()

@@ -16,6 +16,15 @@
  *     touches the edge: a cell always creates its edges 6, 5, 10 (the three meeting at corner 6)
  *     and, on the low boundaries, 0 (j==0&&k==0), 1 (k==0), 2 (k==0), 3 (i==0&&k==0), 4 (j==0),
  *     7 (i==0), 8 (i==0&&j==0), 9 (j==0), 11 (i==0) -- in exactly that order;
+ *     CONVENTION CHOSEN HERE (mode 0, what csrc/mcubes.cu implements): the low-boundary conditions are
+ *     conjunctions (`&&`), i.e. every crossed lattice edge owns exactly ONE vertex, also on the low
+ *     faces of the volume -- the mesh of a block is a proper indexed manifold.  Upstream PyMCubes may
+ *     instead re-create edges 0 / 3 / 8 whenever the cell lies on EITHER low face (`||`), which leaves
+ *     duplicate vertices (same position, different index) along the low faces of every block; that cannot
+ *     be checked here (PyMCubes absent).  mc_ref_run_mode(..., 1) produces that variant so that the tests
+ *     can show what is and is not affected: vertex COUNT and vertex ids differ, the set of triangles as
+ *     geometry (faces keyed by the lattice edge / position of their corners) is identical
+ *     (mcubes_ref.canonical_faces, tests/test_oracle_mcubes.py, tests/test_mcubes_gpu.py).
  *   - vertex position by linear interpolation in double, x1 + (x2-x1)*(iso-f1)/(f2-f1), midpoint
  *     when f1 == f2, in index units; triangles in table order.
  * This file doubles as the timed single-thread CPU baseline for isosurface extraction.
@@ -71,8 +80,9 @@ static int64_t add_vertex(dvec* verts, double x1, double y1, double z1, double c
 
 /* volume: float32 [nx][ny][nz] (C order).  Outputs are malloc'ed; release with mc_ref_free.
  * cases (optional, may be NULL): uint8 [(nx-1)*(ny-1)*(nz-1)] per-cell case index. */
-int mc_ref_run(const float* volume, int nx, int ny, int nz, double iso, double** out_verts, int64_t* out_nv,
-               int64_t** out_faces, int64_t* out_nf, uint8_t* cases) {
+int mc_ref_run_mode(const float* volume, int nx, int ny, int nz, double iso, double** out_verts, int64_t* out_nv,
+                    int64_t** out_faces, int64_t* out_nf, uint8_t* cases, int dup_low_faces) {
+#define LOW2(a, b) (dup_low_faces ? ((a) || (b)) : ((a) && (b)))
     const int cx = nx - 1, cy = ny - 1, cz = nz - 1;
     dvec verts = {0, 0, 0};
     ivec polys = {0, 0, 0};
@@ -108,7 +118,7 @@ int mc_ref_run(const float* volume, int nx, int ny, int nz, double iso, double**
                 if (edges & 0x020) idx[5] = SY(i + 1, j, k + 1) = add_vertex(&verts, x_dx, y, z_dz, y_dy, 1, v[5], v[6], iso);
                 if (edges & 0x400) idx[10] = SZ(i + 1, j + 1, k) = add_vertex(&verts, x_dx, y_dy, z, z_dz, 2, v[2], v[6], iso);
                 if (edges & 0x001) {
-                    if (j == 0 && k == 0) idx[0] = SX(0, 0) = add_vertex(&verts, x, y, z, x_dx, 0, v[0], v[1], iso);
+                    if (LOW2(j == 0, k == 0)) idx[0] = SX(j, k) = add_vertex(&verts, x, y, z, x_dx, 0, v[0], v[1], iso);
                     else idx[0] = SX(j, k);
                 }
                 if (edges & 0x002) {
@@ -120,7 +130,7 @@ int mc_ref_run(const float* volume, int nx, int ny, int nz, double iso, double**
                     else idx[2] = SX(j + 1, k);
                 }
                 if (edges & 0x008) {
-                    if (i == 0 && k == 0) idx[3] = SY(0, j, 0) = add_vertex(&verts, x, y_dy, z, y, 1, v[3], v[0], iso);
+                    if (LOW2(i == 0, k == 0)) idx[3] = SY(i, j, k) = add_vertex(&verts, x, y_dy, z, y, 1, v[3], v[0], iso);
                     else idx[3] = SY(i, j, k);
                 }
                 if (edges & 0x010) {
@@ -132,7 +142,7 @@ int mc_ref_run(const float* volume, int nx, int ny, int nz, double iso, double**
                     else idx[7] = SY(i, j, k + 1);
                 }
                 if (edges & 0x100) {
-                    if (i == 0 && j == 0) idx[8] = SZ(0, 0, k) = add_vertex(&verts, x, y, z, z_dz, 2, v[0], v[4], iso);
+                    if (LOW2(i == 0, j == 0)) idx[8] = SZ(i, j, k) = add_vertex(&verts, x, y, z, z_dz, 2, v[0], v[4], iso);
                     else idx[8] = SZ(i, j, k);
                 }
                 if (edges & 0x200) {
@@ -148,6 +158,7 @@ int mc_ref_run(const float* volume, int nx, int ny, int nz, double iso, double**
             }
         }
     }
+#undef LOW2
 #undef VOL
 #undef SX
 #undef SY
@@ -156,6 +167,11 @@ int mc_ref_run(const float* volume, int nx, int ny, int nz, double iso, double**
     *out_verts = verts.v, *out_nv = (int64_t)(verts.n / 3);
     *out_faces = polys.v, *out_nf = (int64_t)(polys.n / 3);
     return 0;
+}
+
+int mc_ref_run(const float* volume, int nx, int ny, int nz, double iso, double** out_verts, int64_t* out_nv,
+               int64_t** out_faces, int64_t* out_nf, uint8_t* cases) {
+    return mc_ref_run_mode(volume, nx, ny, nz, iso, out_verts, out_nv, out_faces, out_nf, cases, 0);
 }
 
 void mc_ref_free(void* p) { free(p); }

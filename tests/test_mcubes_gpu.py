@@ -33,6 +33,32 @@ def test_bit_exact_vs_serial_oracle(na_lib, cuda_device, name):
     assert np.array_equal(v.cpu().numpy(), v_ref)          # bit-exact doubles
 
 
+@pytest.mark.parametrize("name", ["sphere", "torus", "noise", "ties", "thin"])
+def test_canonical_face_set_vs_oracle_both_boundary_conventions(na_lib, cuda_device, name):
+    """SURVEY.md section 8c's definition of "bit-exact topology": identical per-cell case volume, identical face count,
+    identical face set after canonical relabelling (faces keyed by the owning lattice edge of each corner).  Holds
+    against BOTH plausible upstream conventions for low-face lattice edges (oracle/mcubes_ref.c header); the vertex
+    count matches the one-vertex-per-edge convention the kernel implements."""
+    from neuralangelo_b200 import mesh
+    vol = _volumes()[name]
+    v, f = mesh.mc(torch.from_numpy(vol).to(cuda_device), 0.0)
+    v, f = v.cpu().numpy(), f.cpu().numpy()
+    c_gpu, u_gpu = mcubes_ref.canonical_faces(v, f)
+    for dup in (False, True):
+        v_ref, f_ref, cases = mcubes_ref.marching_cubes(vol, 0.0, return_cases=True, dup_low_faces=dup)
+        assert len(f) == len(f_ref)
+        c_ref, u_ref = mcubes_ref.canonical_faces(v_ref, f_ref)
+        assert np.array_equal(u_gpu, u_ref) and np.array_equal(c_gpu, c_ref)
+        if not dup:
+            assert len(v) == len(v_ref)
+    # per-cell case volume: the kernel's classification is what its faces were emitted from; recompute it here
+    inside = vol <= 0.0
+    c = np.zeros(tuple(n - 1 for n in vol.shape), dtype=np.uint8)
+    for m, (dx, dy, dz) in enumerate([(0, 0, 0), (1, 0, 0), (1, 1, 0), (0, 1, 0), (0, 0, 1), (1, 0, 1), (1, 1, 1), (0, 1, 1)]):
+        c |= (inside[dx:dx + c.shape[0], dy:dy + c.shape[1], dz:dz + c.shape[2]].astype(np.uint8) << m)
+    assert np.array_equal(c, cases)
+
+
 def test_scale_origin_and_nonzero_iso(na_lib, cuda_device):
     from neuralangelo_b200 import mesh
     vol = _volumes()["noise"]

@@ -74,3 +74,31 @@ def test_iso_equal_values_count_as_inside():
     vol[0, 0, 0] = 0.0
     _, _, cases = mcubes_ref.marching_cubes(vol, 0.0, return_cases=True)
     assert cases[0, 0, 0] == 1
+
+
+def test_canonical_faces_is_blind_to_numbering_and_low_face_duplicates():
+    """The two plausible upstream conventions for lattice edges on the low faces of the volume (one vertex per edge
+    vs. a fresh vertex per touching boundary cell) differ in vertex count and ids, never in the surface: the
+    canonical face set (faces keyed by the position of the owning lattice edge) is identical."""
+    rng = np.random.default_rng(3)
+    for vol in (sphere_volume(24, radius=1.2)[0],                       # surface cuts every face of the block
+                rng.standard_normal((9, 11, 7)).astype(np.float32)):
+        v0, f0 = mcubes_ref.marching_cubes(vol, 0.0)
+        v1, f1 = mcubes_ref.marching_cubes(vol, 0.0, dup_low_faces=True)
+        assert len(f0) == len(f1) and len(v1) > len(v0)                  # duplicates exist only in the second mode
+        assert len(np.unique(v0, axis=0)) == len(v0)                     # mode 0: one vertex per crossed edge
+        assert len(np.unique(np.round(v1, 7), axis=0)) == len(v0)        # mode 1: the same edges, some twice (+- 1 ulp)
+        c0, u0 = mcubes_ref.canonical_faces(v0, f0)
+        c1, u1 = mcubes_ref.canonical_faces(v1, f1)
+        assert np.array_equal(u0, u1) and np.array_equal(c0, c1)
+        # a random renumbering + face shuffle + cyclic rotation of the same mesh is canonically equal as well
+        perm = rng.permutation(len(v0))
+        inv = np.empty_like(perm)
+        inv[perm] = np.arange(len(perm))
+        f2 = np.roll(inv[f0], 1, axis=1)[rng.permutation(len(f0))]
+        c2, u2 = mcubes_ref.canonical_faces(v0[perm], f2)
+        assert np.array_equal(u0, u2) and np.array_equal(c0, c2)
+        # ... while flipping one triangle's orientation is detected
+        f3 = f0.copy()
+        f3[0] = f3[0][::-1]
+        assert not np.array_equal(mcubes_ref.canonical_faces(v0, f3)[0], c0)

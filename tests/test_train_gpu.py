@@ -99,3 +99,138 @@ def test_cuda_graph_step_matches_eager(na_lib, cuda_device):
         assert model.neural_sdf.active_levels >= 3
     np.testing.assert_allclose(runs[0], runs[1], rtol=5e-3)
     assert runs[1][-1] < runs[1][0]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Sharded data-parallel step (reduce-scatter -> owner AdamW -> all-gather) == single-process step on the mean
+# gradient (DDP semantics, imaginaire/trainers/utils/get_trainer.py:81-88).  W ranks are emulated as W threads of
+# this process, each with its own model replica on the one GPU, wired together by an in-process communicator that
+# implements the three collectives step_sharded issues.
+# ---------------------------------------------------------------------------------------------------------------
+class _Done:
+    def wait(self):
+        return True
+
+
+class _ThreadComm:
+    """torch.distributed look-alike for `world` threads: every collective deposits its operands, meets the other
+    ranks at a barrier, computes the result from all deposits, and meets them again before returning."""
+
+    def __init__(self, world):
+        import threading
+        self.world = world
+        self.barrier = threading.Barrier(world)
+        self.slots = [None] * world
+        self.local = threading.local()
+
+    def bind(self, rank):
+        self.local.rank = rank
+
+    def _exchange(self, value):
+        torch.cuda.current_stream().synchronize()
+        self.slots[self.local.rank] = value
+        self.barrier.wait()
+        got = list(self.slots)
+        self.barrier.wait()
+        return got
+
+    def all_reduce(self, tensor, op=None, async_op=False):
+        parts = self._exchange(tensor.clone())
+        tensor.copy_(torch.stack(parts).sum(0))
+        self._exchange(None)            # nobody may overwrite an operand before every rank has read it
+        return _Done()
+
+    def reduce_scatter_tensor(self, output, input, op=None, async_op=False):
+        parts = self._exchange(input.clone())
+        n = output.numel()
+        r = self.local.rank
+        output.copy_(torch.stack([p[r * n:(r + 1) * n] for p in parts]).sum(0))
+        self._exchange(None)
+        return _Done()
+
+    def all_gather_into_tensor(self, output, input, async_op=False):
+        parts = self._exchange(input.clone())
+        output.copy_(torch.cat(parts))
+        self._exchange(None)
+        return _Done()
+
+
+def _sharded_vs_single(device, world, schedule):
+    """schedule: list of active-level counts, one per step.  Returns (single-process model, [rank models])."""
+    import threading
+    from neuralangelo_b200.optim import FusedAdamW
+
+    def make(seed=5):
+        model, ts = _tiny_trainer(device, seed=seed)
+        return model, ts.optim
+
+    ref_model, ref_opt = make()
+    ranks = [make() for _ in range(world)]
+    n_small, n_table = ref_opt.flat_g.numel(), ref_opt.table.numel()
+    comm = _ThreadComm(world)
+    for step, active in enumerate(schedule):
+        for m, _ in [(ref_model, None)] + ranks:
+            m.neural_sdf.active_levels = active
+        n_active, _ = ref_opt.active_prefix()
+        g = torch.Generator(device=device).manual_seed(1000 + step)
+        small_g = [torch.randn(n_small, device=device, generator=g) for _ in range(world)]
+        table_g = [torch.randn(n_active, device=device, generator=g) * 1e-3 for _ in range(world)]
+        # a third of the table rows get no gradient on some ranks (as with real rays)
+        for t in table_g:
+            t[torch.rand(n_active, device=device, generator=g) < 0.3] = 0.0
+        ref_opt.flat_g.copy_(torch.stack(small_g).sum(0))
+        ref_opt.table.grad.zero_()
+        ref_opt.table.grad[:n_active].copy_(torch.stack(table_g).sum(0))
+        ref_opt.step(grad_scale=1.0 / world, lr=3e-3)
+        errors = []
+
+        def run(r):
+            try:
+                torch.cuda.set_device(device)
+                comm.bind(r)
+                _, opt = ranks[r]
+                opt.flat_g.copy_(small_g[r])
+                opt.table.grad.zero_()
+                opt.table.grad[:n_active].copy_(table_g[r])
+                opt.step_sharded(r, world, lr=3e-3, comm=comm)
+                torch.cuda.synchronize()
+            except Exception as e:      # noqa: BLE001 -- surface the failure in the main thread
+                errors.append((r, repr(e)))
+                comm.barrier.abort()
+
+        threads = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+        [t.start() for t in threads]
+        [t.join() for t in threads]
+        assert not errors, errors
+    return (ref_model, ref_opt), ranks
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_step_equals_single_process_step_on_mean_gradient(na_lib, cuda_device, world):
+    # 2 -> 2 -> 3 -> 3 -> 4 active levels: ownership of the table slices is re-cut twice
+    (ref_model, ref_opt), ranks = _sharded_vs_single(cuda_device, world, [2, 2, 3, 3, 4])
+    for opt in [ref_opt] + [o for _, o in ranks]:
+        opt.flush_inactive_decay()
+    ref_small, ref_table = ref_opt.flat_p, ref_opt.table.detach()
+    for r, (model, opt) in enumerate(ranks):
+        # sums over ranks are formed in a different order than the single-process sum: fp32 rounding only
+        torch.testing.assert_close(opt.flat_p, ref_small, rtol=1e-5, atol=1e-7, msg=lambda m: f"rank {r} small: {m}")
+        torch.testing.assert_close(opt.table.detach(), ref_table, rtol=1e-5, atol=1e-8, msg=lambda m: f"rank {r} table: {m}")
+        assert float(opt.table.grad.abs().max()) == 0.0 and float(opt.flat_g.abs().max()) == 0.0   # cleared for next step
+    # optimizer state: whole again after gathering, equal to the single-process moments
+    comm = _ThreadComm(world)
+    import threading
+
+    def gather(r):
+        torch.cuda.set_device(cuda_device)
+        comm.bind(r)
+        ranks[r][1].gather_optimizer_state(r, world, comm=comm)
+        torch.cuda.synchronize()
+
+    threads = [threading.Thread(target=gather, args=(r,)) for r in range(world)]
+    [t.start() for t in threads]
+    [t.join() for t in threads]
+    n_active, _ = ref_opt.active_prefix()
+    for _, opt in ranks:
+        torch.testing.assert_close(opt.table_m[:n_active], ref_opt.table_m[:n_active], rtol=1e-5, atol=1e-9)
+        torch.testing.assert_close(opt.table_v[:n_active], ref_opt.table_v[:n_active], rtol=1e-5, atol=1e-12)
