@@ -20,6 +20,7 @@
 #include "na_common.cuh"
 #include <math.h>
 #include <stdlib.h>
+#include <type_traits>
 
 namespace {
 
@@ -315,7 +316,7 @@ hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
                          int64_t n_points, na_unit_map map, uint32_t active_levels,
                          const __grid_constant__ TapParams taps, const float* __restrict__ dout,
                          int64_t dout_stride, int64_t dout_tap_stride, int64_t dout_level_stride,
-                         float* __restrict__ dtable, const Mapping m) {
+                         float* __restrict__ dtable, const Mapping m, const uint32_t level_base) {
     using S = Shape<F>;
     using VT = Vec<S::V>;
     __shared__ LevelS sl[NA_MAX_LEVELS];
@@ -324,7 +325,7 @@ hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
     const int sub = lane % S::LPP;
     const int lvl_in_pass = (lane / S::LPP) % m.levels_per_pass;
     const int pt_in_warp = lane / (S::LPP * m.levels_per_pass);
-    const uint32_t level = blockIdx.y * m.levels_per_pass + lvl_in_pass;
+    const uint32_t level = level_base + blockIdx.y * m.levels_per_pass + lvl_in_pass;
     if (pt_in_warp >= m.points_per_warp || level >= active_levels) return;
     const Level L = make_level<F>(sl[level], dtable);
     float* tb = const_cast<float*>(L.base) + sub * S::V;
@@ -401,6 +402,347 @@ hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
     }
 }
 
+// =============================================================================================
+// Axis-factorised kernels (8 features per level; one evaluation, or centre + six axis-aligned taps in the order
+// +x -x +y -y +z -z that NeuralSDF.compute_gradients uses, modules.py:135-143).
+//
+// The kernels above spend their time issuing instructions, not moving bytes (4.2 G warp instructions per 7-tap
+// call: two lanes per point each recompute seven cells and 56 corner weights).  Here the trilinear weights W(k) = X[kx] Y[ky] Z[kz] are used in factorised form:
+// an axis tap changes a single factor, so with P_x[s] = sum_{ky,kz} Y[ky] Z[kz] row(s,ky,kz) (s = slot along x;
+// P_y, P_z alike) every x-tap that stays in the cell is X'[0] P_x[0] + X'[1] P_x[1]: 16 FMAs instead of 64 + the
+// weights.  A tap that crosses into the neighbouring cell along its axis needs ONE more slot (s = 2 or s = -1):
+// four new rows, the other four are the shared face -- which is also what halves the extra reductions of the
+// backward on fine levels.  Taps further away (epsilon larger than a cell: the start of training on fine levels)
+// fall back to a full eight-corner evaluation.  The backward is the exact transpose: per-axis slot sums of the
+// upstream gradients, then one pair of 16-byte reductions per row.
+// =============================================================================================
+constexpr int kAxisPoints = 1024;   // points per CTA and level (8 per lane pair)
+
+struct AxisTaps {
+    float off0[3];   // offset of tap 0
+    float d[6];      // signed offset of tap t = 1..6 along axis (t - 1) / 2
+};
+
+// Two lanes per point, each with one 16-byte half of the level's 8 features: the pair's loads / stores / reductions
+// of a row are then ONE full 32-byte sector request (a single lane issuing both halves in two instructions doubles
+// the L2 request count, which is what bounds the scattered accesses -- measured, profiles/r02_hashgrid.md).
+using F8 = float4;
+__device__ __forceinline__ F8 f8_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+__device__ __forceinline__ void f8_axpy(F8& a, float w, const F8& v) { axpy4(a, w, v); }
+__device__ __forceinline__ F8 f8_scale(float w, const F8& v) { return make_float4(w * v.x, w * v.y, w * v.z, w * v.w); }
+__device__ __forceinline__ F8 f8_load_keep(const float* p, uint64_t pol) { return na::ldg_f4_hint(p, pol); }
+__device__ __forceinline__ F8 f8_load_stream(const float* p, uint64_t pol) { return na::ldg_f4_stream_hint(p, pol); }
+__device__ __forceinline__ void f8_store_stream(float* p, const F8& v, uint64_t pol) { na::st_f4_hint(p, v, pol); }
+__device__ __forceinline__ void f8_red(float* p, const F8& v, uint64_t pol) { na::red_add_f4_hint(p, v, pol); }
+
+struct AxisCell {
+    uint32_t c[3];   // cell of tap 0
+    int ci[3];       // the same as signed integers (for the cell distance of a tap)
+    float W[3][2];   // {1 - w, w} per axis
+};
+
+__device__ __forceinline__ AxisCell axis_locate(const Level& L, const na_unit_map& map, const AxisTaps& taps,
+                                                const float (&xs)[3]) {
+    AxisCell A;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const float p = fmaf(L.scale, (xs[d] + taps.off0[d] - map.vol_min) * map.inv_extent, 0.5f);
+        const float fl = floorf(p);
+        A.ci[d] = (int)fl;
+        A.c[d] = (uint32_t)A.ci[d];
+        const float w = p - fl;
+        A.W[d][0] = 1.f - w, A.W[d][1] = w;
+    }
+    return A;
+}
+
+// position of tap (axis a, signed offset d) along its axis: cell distance from tap 0's cell and weight in its own cell
+__device__ __forceinline__ void axis_tap(const Level& L, const na_unit_map& map, float xa, float d, int ci, int& delta,
+                                         float& w, uint32_t& cell) {
+    const float p = fmaf(L.scale, (xa + d - map.vol_min) * map.inv_extent, 0.5f);
+    const float fl = floorf(p);
+    const int c = (int)fl;
+    delta = c - ci;
+    cell = (uint32_t)c;
+    w = p - fl;
+}
+
+// row index for cell offsets (along axis A: sa; the two other axes B, C: sb, sc) from tap 0's cell
+template <int A>
+__device__ __forceinline__ uint32_t axis_row(const Level& L, const AxisCell& C, uint32_t ca, int sb, int sc) {
+    constexpr int B = (A + 1) % 3, Cc = (A + 2) % 3;
+    uint32_t cc[3];
+    cc[A] = ca;
+    cc[B] = C.c[B] + (uint32_t)sb;
+    cc[Cc] = C.c[Cc] + (uint32_t)sc;
+    return entry_index(L, cc[0], cc[1], cc[2]);
+}
+
+// ---- forward: ONE lane per point and level, whole 32-byte rows per lane -------------------------------------
+// sm_100 has 256-bit global loads and stores (LDG.256 / STG.256): a lane fetches a table row, or writes a tap's 8
+// features, as one full-sector request -- no second lane that would have to repeat the cell arithmetic.
+struct R8 {
+    float v[8];
+};
+__device__ __forceinline__ R8 r8_zero() {
+    R8 r;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r.v[i] = 0.f;
+    return r;
+}
+__device__ __forceinline__ void r8_axpy(R8& a, float w, const R8& b) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a.v[i] = fmaf(w, b.v[i], a.v[i]);
+}
+__device__ __forceinline__ R8 r8_scale(float w, const R8& b) {
+    R8 r;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r.v[i] = w * b.v[i];
+    return r;
+}
+__device__ __forceinline__ R8 r8_load_keep(const float* p, uint64_t pol) {
+    R8 r;
+    asm volatile("ld.global.nc.L2::cache_hint.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
+                 : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]),
+                   "=f"(r.v[7])
+                 : "l"(p), "l"(pol));
+    return r;
+}
+__device__ __forceinline__ void r8_store_stream(float* p, const R8& r, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8}, %9;" ::"l"(p), "f"(r.v[0]), "f"(r.v[1]),
+                 "f"(r.v[2]), "f"(r.v[3]), "f"(r.v[4]), "f"(r.v[5]), "f"(r.v[6]), "f"(r.v[7]), "l"(pol)
+                 : "memory");
+}
+
+template <int NT>
+__global__ void __launch_bounds__(kThreads, 2)
+hashgrid_axis_fwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ table,
+                         const float* __restrict__ x, int64_t n_points, na_unit_map map, uint32_t active_levels,
+                         const AxisTaps taps, float* __restrict__ out, int64_t out_stride, int64_t out_tap_stride,
+                         int64_t out_level_stride) {
+    constexpr int F = 8;
+    __shared__ LevelS sl[NA_MAX_LEVELS];
+    stage_levels(desc, sl);
+    const uint32_t level = blockIdx.y;
+    const uint64_t keep = na::policy_evict_last(), stream = na::policy_evict_first();
+    const Level L = make_level<F>(sl[level], table);
+    // a CTA owns kAxisPoints consecutive points of one level; its 256 lanes stride over them
+    const int64_t cta_base = (int64_t)blockIdx.x * kAxisPoints;
+#pragma unroll 1
+    for (int it = 0; it < kAxisPoints / kThreads; ++it) {
+        const int64_t n = cta_base + it * kThreads + threadIdx.x;
+        if (n >= n_points) break;
+        float* o = out + n * out_stride + level * out_level_stride;
+        if (level >= active_levels) {   // coarse-to-fine mask: inactive levels are exactly zero
+#pragma unroll
+            for (int t = 0; t < NT; ++t) r8_store_stream(o + t * out_tap_stride, r8_zero(), stream);
+            continue;
+        }
+        const float xs[3] = {__ldg(x + n * 3 + 0), __ldg(x + n * 3 + 1), __ldg(x + n * 3 + 2)};
+        const AxisCell C = axis_locate(L, map, taps, xs);
+        // the eight rows of the cell, folded into the per-axis slot sums (two batches of four rows in flight)
+        R8 P[3][2];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) P[a][0] = r8_zero(), P[a][1] = r8_zero();
+#pragma unroll
+        for (int kz = 0; kz < 2; ++kz) {
+            R8 r[2][2];
+#pragma unroll
+            for (int ky = 0; ky < 2; ++ky)
+#pragma unroll
+                for (int kx = 0; kx < 2; ++kx) {
+                    const uint32_t idx = entry_index(L, C.c[0] + kx, C.c[1] + ky, C.c[2] + kz);
+                    r[ky][kx] = r8_load_keep(L.base + (size_t)idx * F, keep);
+                }
+#pragma unroll
+            for (int ky = 0; ky < 2; ++ky)
+#pragma unroll
+                for (int kx = 0; kx < 2; ++kx) {
+                    r8_axpy(P[0][kx], C.W[1][ky] * C.W[2][kz], r[ky][kx]);
+                    r8_axpy(P[1][ky], C.W[0][kx] * C.W[2][kz], r[ky][kx]);
+                    r8_axpy(P[2][kz], C.W[0][kx] * C.W[1][ky], r[ky][kx]);
+                }
+        }
+        {
+            R8 v = r8_scale(C.W[0][0], P[0][0]);
+            r8_axpy(v, C.W[0][1], P[0][1]);
+            r8_store_stream(o, v, stream);
+        }
+        if (NT == 1) continue;
+        // Taps that stay in the cell are written at once; the others are collected and served one per round so that a
+        // warp needs max-over-lanes rounds (a dependent memory round trip each), not one per tap index.
+        uint32_t crossing = 0;
+#pragma unroll
+        for (int t = 1; t < 7; ++t) {
+            const int A = (t - 1) >> 1;
+            int delta;
+            float w;
+            uint32_t cell;
+            axis_tap(L, map, xs[A], taps.d[t - 1], C.ci[A], delta, w, cell);
+            if (delta == 0) {
+                R8 v = r8_scale(1.f - w, P[A][0]);
+                r8_axpy(v, w, P[A][1]);
+                r8_store_stream(o + t * out_tap_stride, v, stream);
+            } else {
+                crossing |= 1u << t;
+            }
+        }
+        while (crossing) {
+            const int t = __ffs(crossing) - 1;
+            crossing &= crossing - 1;
+            const int a = (t - 1) >> 1;
+            const float xa = a == 0 ? xs[0] : (a == 1 ? xs[1] : xs[2]);
+            const int cia = a == 0 ? C.ci[0] : (a == 1 ? C.ci[1] : C.ci[2]);
+            int delta;
+            float w;
+            uint32_t cell;
+            axis_tap(L, map, xa, taps.d[t - 1], cia, delta, w, cell);
+            float wb[2], wc[2];   // weights of the two other axes in cyclic order b = a + 1, c = a + 2
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                wb[k] = a == 0 ? C.W[1][k] : (a == 1 ? C.W[2][k] : C.W[0][k]);
+                wc[k] = a == 0 ? C.W[2][k] : (a == 1 ? C.W[0][k] : C.W[1][k]);
+            }
+            auto face = [&](uint32_t ca) {   // sum over the four rows of the face at coordinate ca along axis a
+                R8 r[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    uint32_t cc[3];
+#pragma unroll
+                    for (int d = 0; d < 3; ++d) {
+                        const int rel = (d - a + 3) % 3;
+                        cc[d] = rel == 0 ? ca : C.c[d] + (uint32_t)(rel == 1 ? (q & 1) : (q >> 1));
+                    }
+                    r[q] = r8_load_keep(L.base + (size_t)entry_index(L, cc[0], cc[1], cc[2]) * F, keep);
+                }
+                R8 e = r8_zero();
+#pragma unroll
+                for (int q = 0; q < 4; ++q) r8_axpy(e, wb[q & 1] * wc[q >> 1], r[q]);
+                return e;
+            };
+            R8 v;
+            if (delta == 1 || delta == -1) {   // neighbouring cell: one face is shared with tap 0's cell (slot sums P)
+                const bool up = delta > 0;
+                const R8 s0 = up ? P[0][1] : P[0][0], s1 = up ? P[1][1] : P[1][0], s2 = up ? P[2][1] : P[2][0];
+                const R8 shared = a == 0 ? s0 : (a == 1 ? s1 : s2);
+                const R8 e = face(up ? cell + 1u : cell);
+                v = r8_scale(up ? 1.f - w : w, shared);
+                r8_axpy(v, up ? w : 1.f - w, e);
+            } else {                           // further away (epsilon larger than this level's cells): both faces
+                const R8 e0 = face(cell), e1 = face(cell + 1u);
+                v = r8_scale(1.f - w, e0);
+                r8_axpy(v, w, e1);
+            }
+            r8_store_stream(o + t * out_tap_stride, v, stream);
+        }
+    }
+}
+
+template <int NT>
+__global__ void __launch_bounds__(kThreads, 3)
+hashgrid_axis_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ x, int64_t n_points,
+                         na_unit_map map, const AxisTaps taps, const float* __restrict__ dout, int64_t dout_stride,
+                         int64_t dout_tap_stride, int64_t dout_level_stride, float* __restrict__ dtable,
+                         uint32_t level_base) {
+    constexpr int F = 8;
+    __shared__ LevelS sl[NA_MAX_LEVELS];
+    stage_levels(desc, sl);
+    const int sub = threadIdx.x & 1;
+    const uint32_t level = level_base + blockIdx.y;
+    const uint64_t keep = na::policy_evict_last(), stream = na::policy_evict_first();
+    const Level L = make_level<F>(sl[level], dtable);
+    float* tb = const_cast<float*>(L.base) + sub * 4;
+    const int64_t cta_base = (int64_t)blockIdx.x * kAxisPoints;
+#pragma unroll 1
+    for (int it = 0; it < kAxisPoints / (kThreads / 2); ++it) {
+    const int64_t n = cta_base + it * (kThreads / 2) + (threadIdx.x >> 1);
+    if (n >= n_points) break;
+    const float* g = dout + n * dout_stride + level * dout_level_stride + sub * 4;
+    F8 gv[NT];
+#pragma unroll
+    for (int t = 0; t < NT; ++t) gv[t] = f8_load_stream(g + t * dout_tap_stride, stream);
+    const float xs[3] = {__ldg(x + n * 3 + 0), __ldg(x + n * 3 + 1), __ldg(x + n * 3 + 2)};
+    const AxisCell C = axis_locate(L, map, taps, xs);
+    F8 S[3][2];   // per-axis slot sums of the upstream gradients; tap 0 is booked on the x axis
+    S[0][0] = f8_scale(C.W[0][0], gv[0]), S[0][1] = f8_scale(C.W[0][1], gv[0]);
+#pragma unroll
+    for (int a = 1; a < 3; ++a) S[a][0] = f8_zero(), S[a][1] = f8_zero();
+    if (NT > 1) {
+        // four rows of the face at cell coordinate `ca` along axis A receive e, weighted by the other two axes
+        auto face = [&](auto axis_tag, uint32_t ca, const F8& e) {
+            constexpr int A = decltype(axis_tag)::value, B = (A + 1) % 3, Cc = (A + 2) % 3;
+#pragma unroll
+            for (int sc = 0; sc < 2; ++sc)
+#pragma unroll
+                for (int sb = 0; sb < 2; ++sb)
+                    f8_red(tb + (size_t)axis_row<A>(L, C, ca, sb, sc) * F, f8_scale(C.W[B][sb] * C.W[Cc][sc], e), keep);
+        };
+        auto axis_taps = [&](auto axis_tag) {
+            constexpr int A = decltype(axis_tag)::value;
+#pragma unroll
+            for (int sgn = 0; sgn < 2; ++sgn) {
+                const int t = 1 + 2 * A + sgn;
+                int delta;
+                float w;
+                uint32_t cell;
+                axis_tap(L, map, xs[A], taps.d[t - 1], C.ci[A], delta, w, cell);
+                const F8& gt = gv[t < NT ? t : 0];
+                if (delta == 0) {
+                    f8_axpy(S[A][0], 1.f - w, gt);
+                    f8_axpy(S[A][1], w, gt);
+                } else if (delta == 1) {
+                    f8_axpy(S[A][1], 1.f - w, gt);
+                    face(axis_tag, cell + 1u, f8_scale(w, gt));
+                } else if (delta == -1) {
+                    f8_axpy(S[A][0], w, gt);
+                    face(axis_tag, cell, f8_scale(1.f - w, gt));
+                } else {
+                    face(axis_tag, cell, f8_scale(1.f - w, gt));
+                    face(axis_tag, cell + 1u, f8_scale(w, gt));
+                }
+            }
+        };
+        axis_taps(std::integral_constant<int, 0>{});
+        axis_taps(std::integral_constant<int, 1>{});
+        axis_taps(std::integral_constant<int, 2>{});
+    }
+#pragma unroll
+    for (int kz = 0; kz < 2; ++kz)
+#pragma unroll
+        for (int ky = 0; ky < 2; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 2; ++kx) {
+                F8 v = f8_scale(C.W[1][ky] * C.W[2][kz], S[0][kx]);
+                if (NT > 1) {
+                    f8_axpy(v, C.W[0][kx] * C.W[2][kz], S[1][ky]);
+                    f8_axpy(v, C.W[0][kx] * C.W[1][ky], S[2][kz]);
+                }
+                const uint32_t idx = entry_index(L, C.c[0] + kx, C.c[1] + ky, C.c[2] + kz);
+                f8_red(tb + (size_t)idx * F, v, keep);
+            }
+    }
+}
+
+// The axis kernels apply when the level has 8 features, every vector access is 16-byte aligned, and the taps are
+// one evaluation or exactly {tap 0, +-x, +-x, +-y, +-y, +-z, +-z}: tap t >= 1 differs from tap 0 along axis (t-1)/2 only.
+bool axis_taps_from(const TapParams& tp, uint32_t n_features, AxisTaps& at) {
+    if (n_features != 8 || (tp.n != 1 && tp.n != 7)) return false;
+    for (int d = 0; d < 3; ++d) at.off0[d] = tp.off[0][d];
+    for (int t = 1; t < 7; ++t) at.d[t - 1] = 0.f;
+    if (tp.n == 7) {
+        for (int t = 1; t < 7; ++t) {
+            const int a = (t - 1) / 2;
+            for (int d = 0; d < 3; ++d)
+                if (d != a && tp.off[t][d] != tp.off[0][d]) return false;
+            at.d[t - 1] = tp.off[t][a];
+        }
+        // tap 0 sits on the axes the other taps move along: its own offset must not differ from theirs off-axis
+        for (int d = 0; d < 3; ++d)
+            if (tp.off[0][d] != 0.f) return false;
+    }
+    return true;
+}
+
 // levels_per_pass trades HBM write/read efficiency of the feature rows (more levels per warp ->
 // longer contiguous runs per row) against L2 residency of the table (fewer levels in flight ->
 // one 128 MiB hashed level is the working set).  Measured on B200, 2^22 random points, default
@@ -411,6 +753,7 @@ hashgrid_taps_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
 struct DevKnobs {
     int group = 0;   // 0 = default mapping
     int iters = 16;  // points per warp and CTA
+    int generic = 0; // 1 = never take the axis-factorised kernels (A/B measurements)
 };
 const DevKnobs& dev_knobs() {
     static const DevKnobs k = [] {
@@ -418,6 +761,7 @@ const DevKnobs& dev_knobs() {
 #ifdef NA_HG_DEV_KNOBS
         if (const char* e = getenv("NA_HG_GROUP")) v.group = atoi(e) > 0 ? atoi(e) : 0;
         if (const char* e = getenv("NA_HG_ITERS")) v.iters = atoi(e) >= 1 ? (atoi(e) > 4096 ? 4096 : atoi(e)) : 16;
+        if (const char* e = getenv("NA_HG_GENERIC")) v.generic = atoi(e) != 0;
 #endif
         return v;
     }();
@@ -457,6 +801,11 @@ int validate(const na_hashgrid_desc* desc, const void* a, const void* b, int64_t
     return NA_OK;
 }
 
+// whole 8-float rows at 32-byte alignment (the 256-bit accesses of the one-lane-per-point forward)
+bool row_aligned(const void* p, int64_t stride, int64_t tap_stride, int64_t level_stride) {
+    return ((uintptr_t)p % 32 == 0) && (stride % 8 == 0) && (tap_stride % 8 == 0) && (level_stride % 8 == 0);
+}
+
 bool vec_aligned(const void* p, int64_t stride, int64_t tap_stride, int64_t level_stride, int n_features) {
     const int v = n_features >= 4 ? 4 : 2;
     return ((uintptr_t)p % (v * sizeof(float)) == 0) && (stride % v == 0) && (tap_stride % v == 0) &&
@@ -477,6 +826,23 @@ template <int F>
 int launch_fwd(const na_hashgrid_desc* desc, const float* table, const float* x, int64_t n_points, na_unit_map map,
                uint32_t active_levels, const TapParams& tp, float* out, int64_t out_stride, int64_t out_tap_stride,
                int64_t out_level_stride, cudaStream_t stream) {
+    if (F == 8) {
+        AxisTaps at;
+        if (axis_taps_from(tp, F, at) && row_aligned(out, out_stride, out_tap_stride, out_level_stride) &&
+            row_aligned(table, 8, 8, 8) && !dev_knobs().generic) {
+            const int64_t nb = (n_points + kAxisPoints - 1) / kAxisPoints;
+            NA_REQUIRE(nb <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
+            dim3 g((unsigned)nb, desc->n_levels);
+            if (tp.n == 1)
+                hashgrid_axis_fwd_kernel<1><<<g, kThreads, 0, stream>>>(*desc, table, x, n_points, map, active_levels, at,
+                                                                        out, out_stride, out_tap_stride, out_level_stride);
+            else
+                hashgrid_axis_fwd_kernel<7><<<g, kThreads, 0, stream>>>(*desc, table, x, n_points, map, active_levels, at,
+                                                                        out, out_stride, out_tap_stride, out_level_stride);
+            NA_CHECK_LAUNCH("hashgrid_axis_fwd_kernel");
+            return NA_OK;
+        }
+    }
     const Mapping m = make_mapping(desc, desc->n_levels, tp.n, out_level_stride != F);
     const int64_t blocks = (n_points + m.points_per_cta - 1) / m.points_per_cta;
     NA_REQUIRE(blocks <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
@@ -494,20 +860,42 @@ int launch_fwd(const na_hashgrid_desc* desc, const float* table, const float* x,
 template <int F>
 int launch_bwd(const na_hashgrid_desc* desc, const float* x, int64_t n_points, na_unit_map map,
                uint32_t active_levels, const TapParams& tp, const float* dout, int64_t dout_stride,
-               int64_t dout_tap_stride, int64_t dout_level_stride, float* dtable, cudaStream_t stream) {
-    const Mapping m = make_mapping(desc, active_levels, tp.n, dout_level_stride != F);
+               int64_t dout_tap_stride, int64_t dout_level_stride, float* dtable, cudaStream_t stream,
+               uint32_t level_base = 0) {
+    if (level_base >= active_levels) return NA_OK;
+    if (F == 8) {
+        AxisTaps at;
+        if (axis_taps_from(tp, F, at) && vec_aligned(dout, dout_stride, dout_tap_stride, dout_level_stride, F) &&
+            !dev_knobs().generic) {
+            const int64_t nb = (n_points + kAxisPoints - 1) / kAxisPoints;
+            NA_REQUIRE(nb <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
+            dim3 g((unsigned)nb, active_levels - level_base);
+            if (tp.n == 1)
+                hashgrid_axis_bwd_kernel<1><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
+                                                                        dout_tap_stride, dout_level_stride, dtable, level_base);
+            else
+                hashgrid_axis_bwd_kernel<7><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
+                                                                        dout_tap_stride, dout_level_stride, dtable, level_base);
+            NA_CHECK_LAUNCH("hashgrid_axis_bwd_kernel");
+            return NA_OK;
+        }
+    }
+    const Mapping m = make_mapping(desc, active_levels - level_base, tp.n, dout_level_stride != F);
     const int64_t blocks = (n_points + m.points_per_cta - 1) / m.points_per_cta;
     NA_REQUIRE(blocks <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
     dim3 grid((unsigned)blocks, m.passes);
     if (vec_aligned(dout, dout_stride, dout_tap_stride, dout_level_stride, F))
         hashgrid_taps_bwd_kernel<F, true><<<grid, kThreads, 0, stream>>>(
-            *desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dout_level_stride, dtable, m);
+            *desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dout_level_stride, dtable, m,
+            level_base);
     else
         hashgrid_taps_bwd_kernel<F, false><<<grid, kThreads, 0, stream>>>(
-            *desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dout_level_stride, dtable, m);
+            *desc, x, n_points, map, active_levels, tp, dout, dout_stride, dout_tap_stride, dout_level_stride, dtable, m,
+            level_base);
     NA_CHECK_LAUNCH("hashgrid_taps_bwd_kernel");
     return NA_OK;
 }
+
 
 }  // namespace
 

@@ -46,15 +46,16 @@ class _EncodeRows(torch.autograd.Function):
     def forward(ctx, pts, table, module, unit_map, active_levels, taps):
         width = module.n_output_dims
         n, n_taps = pts.shape[0], len(taps)
-        # rows padded to 3+width+1 floats with the pad in FRONT: features start 16 bytes into the row, so the
-        # kernel's 16-byte vector stores apply; the returned view drops the pad column.
-        buf = torch.empty(n_taps, n, width + 4, dtype=torch.float32, device=pts.device)
+        # rows padded to 3+width+5 floats with the pad in FRONT: features start 32 bytes into a row whose stride is a
+        # multiple of 32 bytes (for the default 128 features), so the kernel's whole-row 256-bit stores apply; the
+        # returned view drops the pad columns.
+        buf = torch.empty(n_taps, n, width + 8, dtype=torch.float32, device=pts.device)
         offs = _tap_tensor(taps, pts.device)
-        buf[:, :, 1:4] = pts[None, :, :] + offs[:, None, :]
-        hashgrid.encode_taps(module.desc, table, pts, unit_map, active_levels, taps, out=buf[:, :, 4:])
+        buf[:, :, 5:8] = pts[None, :, :] + offs[:, None, :]
+        hashgrid.encode_taps(module.desc, table, pts, unit_map, active_levels, taps, out=buf[:, :, 8:])
         ctx.save_for_backward(pts)
         ctx.module, ctx.args = module, (unit_map, active_levels, taps)
-        return buf[:, :, 1:]
+        return buf[:, :, 5:]
 
     @staticmethod
     def backward(ctx, drows):

