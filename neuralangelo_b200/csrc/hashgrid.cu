@@ -653,6 +653,8 @@ hashgrid_axis_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
     const Level L = make_level<F>(sl[level], dtable);
     float* tb = const_cast<float*>(L.base) + sub * 4;
     const int64_t cta_base = (int64_t)blockIdx.x * kAxisPoints;
+    // (measured and rejected, profiles/r02_hashgrid.md: prefetching the next point's loads, and a fourth resident CTA,
+    //  both slow this kernel down -- it is bound by the L2's reduction throughput, more requests in flight only queue)
 #pragma unroll 1
     for (int it = 0; it < kAxisPoints / (kThreads / 2); ++it) {
     const int64_t n = cta_base + it * (kThreads / 2) + (threadIdx.x >> 1);
@@ -870,7 +872,7 @@ int launch_bwd(const na_hashgrid_desc* desc, const float* x, int64_t n_points, n
             const int64_t nb = (n_points + kAxisPoints - 1) / kAxisPoints;
             NA_REQUIRE(nb <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
             dim3 g((unsigned)nb, active_levels - level_base);
-            if (tp.n == 1)
+if (tp.n == 1)
                 hashgrid_axis_bwd_kernel<1><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
                                                                         dout_tap_stride, dout_level_stride, dtable, level_base);
             else
