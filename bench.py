@@ -176,6 +176,8 @@ def run_reference(args, rank, world):
                                    "GB/s = full-size algorithmic bytes x (sample/full) / seconds"},
         "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "note": "host-core throughput of the CPU port; it does not depend on the job size, so at --gpus N (weak scaling: "
+                "N x the points) the same figure stands beside the N-GPU aggregate",
     }
     print(json.dumps(line), flush=True)
 
@@ -349,11 +351,12 @@ def _look_at(eye):
     return torch.cat([R, (-R @ eye)[:, None]], dim=1)
 
 
-def extra_train_step(rank, world, dev, steps=30, warmup=8, taps=4, force_all_levels=True):
+def extra_train_step(rank, world, dev, steps=200, warmup=50, taps=4, force_all_levels=True, table_exchange="auto"):
     """BASELINE.json configs[2]/[3]: full training step of the default hash-grid config (16 levels, 2^22, dim 8),
     synthetic cameras (32 poses on a radius-3 sphere, 800x800, focal 1111), random-init weights, 512 rays per
     GPU per step, batch pose/intrinsics/ray indices/target colours arriving from pinned host memory, gradients
-    all-reduced across ranks.  Returns aggregate rays/s."""
+    exchanged across ranks (median of >= 200 steps after 50 warm-up).  Returns aggregate rays/s
+    and the per-phase device times (forward + backward / gradient exchange + optimizer)."""
     from neuralangelo_b200.config import default_data_config, default_model_config
     from neuralangelo_b200.model import Model
     from neuralangelo_b200.trainer import TrainStep
@@ -361,7 +364,7 @@ def extra_train_step(rank, world, dev, steps=30, warmup=8, taps=4, force_all_lev
     cfg = default_model_config()
     cfg.object.sdf.gradient.taps = taps
     model = Model(cfg, default_data_config()).to(dev)
-    ts = TrainStep(model, max_iter=500000, warm_up_end=5000, use_cuda_graph=True)
+    ts = TrainStep(model, max_iter=500000, warm_up_end=5000, use_cuda_graph=True, table_exchange=table_exchange)
     if force_all_levels:
         ts.current_iteration = 5000 + 16 * 5000
     g = torch.Generator().manual_seed(1000 + rank)
@@ -384,23 +387,36 @@ def extra_train_step(rank, world, dev, steps=30, warmup=8, taps=4, force_all_lev
     if world > 1:
         torch.distributed.barrier()
     torch.cuda.synchronize()
+    ts.record_phases, ts.phase_events = True, []
     t0 = time.perf_counter()
     for i in range(steps):
         loss = step(i)
-    loss_host = float(loss)            # device->host read of the step's result
+    loss_host = float(loss.detach())   # device->host read of the step's result
     if world > 1:
         torch.distributed.barrier()
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / steps
+    ev = ts.phase_events
+    fb = [e[0].elapsed_time(e[1]) for e in ev]
+    ex = [e[1].elapsed_time(e[2]) for e in ev]
+    per_step = [a[0].elapsed_time(b[0]) for a, b in zip(ev[:-1], ev[1:])]      # start to start: the steady-state period
+    med = statistics.median(per_step) * 1e-3
     if world > 1:
-        t = torch.tensor([dt], device=dev, dtype=torch.float64)
+        t = torch.tensor([dt, med, statistics.median(fb), statistics.median(ex)], device=dev, dtype=torch.float64)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-        dt = float(t)
+        dt, med, fb_ms, ex_ms = t.tolist()
+    else:
+        fb_ms, ex_ms = statistics.median(fb), statistics.median(ex)
+    exchange = "none (1 GPU)" if world == 1 else ("multimem: one kernel (NVLink multicast reduce + AdamW + broadcast)"
+                                                  if ts.multimem else "nccl: reduce-scatter / owner AdamW / all-gather")
     del ts, model
     torch.cuda.empty_cache()
-    return {"rays_per_s": 512 * world / dt, "ms_per_step": dt * 1e3, "rays_per_gpu": 512, "taps": taps,
-            "active_levels": 16 if force_all_levels else 4, "last_loss": loss_host, "timing": "host clock around "
-            "synchronised steps, max over ranks; includes H2D of the batch and the gradient all-reduce"}
+    return {"rays_per_s": 512 * world / med, "ms_per_step": med * 1e3, "mean_ms_per_step_host_clock": dt * 1e3,
+            "rays_per_gpu": 512, "taps": taps, "active_levels": 16 if force_all_levels else 4, "steps": steps,
+            "warmup": warmup, "last_loss": loss_host,
+            "phases_ms": {"forward_backward": fb_ms, "exchange_and_optimizer": ex_ms}, "table_exchange": exchange,
+            "timing": "median over steps of the device time between consecutive step starts (CUDA events), max over "
+                      "ranks; includes H2D of the batch, the gradient exchange and the optimizer"}
 
 
 def extra_mesh(rank, world, dev, res=2048):
@@ -546,12 +562,18 @@ def collect_extras(args, rank, world, dev):
     for name, fn in (("sdf_mlp", lambda: extra_sdf_mlp(dev)),
                      ("composite", lambda: extra_composite(dev)),
                      ("train_step", lambda: extra_train_step(rank, world, dev)),
+                     ("train_step_taps6", lambda: extra_train_step(rank, world, dev, taps=6)),
                      ("train_step_4_active_levels", lambda: extra_train_step(rank, world, dev, force_all_levels=False)),
                      ("mesh_extract", lambda: extra_mesh(rank, world, dev))):
         try:
             extras[name] = fn()
         except Exception as e:  # noqa: BLE001 -- extras must never break the headline line
             extras[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    if world > 1:   # the library-collective form of the same step, for comparison with the fused multicast kernel
+        try:
+            extras["train_step_nccl_exchange"] = extra_train_step(rank, world, dev, table_exchange="nccl")
+        except Exception as e:  # noqa: BLE001
+            extras["train_step_nccl_exchange"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     return extras
 
 

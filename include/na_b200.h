@@ -230,6 +230,23 @@ int na_mc_run_static(const float* volume, int nx, int ny, int nz, double iso, do
 int na_adamw_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
                   float beta2, float eps, float weight_decay, int64_t step, float grad_scale, int zero_grad,
                   void* stream);
+
+/* The data-parallel table step as ONE kernel over NVLink multicast (NVSwitch in-fabric reduction): for the slice
+ * [offset, offset + n) this rank owns, gradients of all ranks are summed by multimem.ld_reduce through `mc_grads`,
+ * AdamW runs in registers (same arithmetic as na_adamw_step, grad_scale = 1 / world), the new parameters are written
+ * to every rank with multimem.st through `mc_params`.  Gradients are left as they are: every rank clears its own
+ * buffer after the closing barrier (all ranks have read it by then).  `mc_*` are
+ * MULTICAST virtual addresses of symmetric allocations (e.g. torch.distributed._symmetric_memory rendezvous:
+ * handle.multicast_ptr); params_local / exp_avg / exp_avg_sq are this rank's ordinary device pointers (whole-buffer
+ * bases; the kernel adds `offset`).  The caller must separate the launch from the producers of the gradients and from
+ * the consumers of the parameters with cross-rank barriers on the stream.  max_ctas <= 0 picks the grid; unroll
+ * (2, 4 or 8; 0 = default 4) is the number of multicast loads a thread keeps in flight.
+ * Replaces: DDP's bucketed gradient all-reduce (imaginaire/trainers/utils/get_trainer.py:81-88) + AdamW
+ * (get_trainer.py:106-150) + zero_grad (imaginaire/trainers/base.py:454-457) for the hash table. */
+int na_adamw_step_multimem(float* mc_grads, float* mc_params, const float* params_local, float* exp_avg,
+                           float* exp_avg_sq, int64_t offset, int64_t n, float lr, float beta1, float beta2,
+                           float eps, float weight_decay, int64_t step, float grad_scale, int max_ctas, int unroll,
+                           void* stream);
 /* params[i] *= factor: applies the accumulated weight decay of hash-grid levels that were inactive
  * (zero gradient, zero moments: AdamW reduces to p *= 1 - lr*wd per step) when they become active. */
 int na_scale_inplace(float* params, int64_t n, float factor, void* stream);

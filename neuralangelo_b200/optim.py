@@ -75,16 +75,11 @@ class FusedAdamW:
         n_active, _ = self.active_prefix()
         return self.flat_g, self.table.grad[:n_active]
 
-    def step(self, grad_scale=1.0, lr=None, table_chunks=None, small_ready=None):
-        """One optimizer step.  `table_chunks`: optional list of (lo, hi, wait_fn) covering the active table prefix;
-        each chunk's update is issued after wait_fn() (its gradient all-reduce), so the update of chunk i overlaps
-        the all-reduce of chunk i+1 running on the communication stream.  `small_ready` likewise gates the flat
-        bucket."""
+    def step(self, grad_scale=1.0, lr=None):
+        """One optimizer step on this rank's (already reduced) gradients."""
         lr = self.lr if lr is None else lr
         self.step_count += 1
         b1, b2 = self.betas
-        if small_ready is not None:
-            small_ready()
         stream = _lib.current_stream()
         _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
                                       self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
@@ -106,16 +101,9 @@ class FusedAdamW:
                 _lib.check(_L().na_scale_inplace(ptr(self.table[lo:]), hi - lo, math.exp(self.pending_log_decay), stream),
                            "na_scale_inplace")
             self.applied_levels = active
-        chunks = list(table_chunks) if table_chunks else [(0, n_active, None)]
-        assert chunks[0][0] == 0, "table_chunks must start at 0"
-        if chunks[-1][1] < n_active:      # eager (non-lazy) mode also steps the levels beyond the reduced prefix
-            chunks.append((chunks[-1][1], n_active, None))
-        for lo, hi, wait_fn in chunks:
-            if wait_fn is not None:
-                wait_fn()
-            _lib.check(_L().na_adamw_step(ptr(self.table[lo:]), ptr(self.table.grad[lo:]), ptr(self.table_m[lo:]),
-                                          ptr(self.table_v[lo:]), hi - lo, lr, b1, b2, self.eps, self.weight_decay,
-                                          self.step_count, grad_scale, 1, stream), "na_adamw_step")
+        _lib.check(_L().na_adamw_step(ptr(self.table), ptr(self.table.grad), ptr(self.table_m), ptr(self.table_v),
+                                      n_active, lr, b1, b2, self.eps, self.weight_decay, self.step_count, grad_scale, 1,
+                                      stream), "na_adamw_step")
         if self.lazy and self.applied_levels < self.n_levels:
             self.pending_log_decay += math.log1p(-lr * self.weight_decay)
 
@@ -167,6 +155,80 @@ class FusedAdamW:
         if b < n_active:
             g[b:n_active].zero_()
         ag.wait()
+        sdf_mod = getattr(self.model, "neural_sdf", None)
+        if sdf_mod is not None and hasattr(sdf_mod, "invalidate_packed_weights"):
+            sdf_mod.invalidate_packed_weights()
+        if self.lazy and self.applied_levels < self.n_levels:
+            self.pending_log_decay += math.log1p(-lr * self.weight_decay)
+
+    # ---- NVLink-multicast path: reduce-scatter + AdamW + all-gather in one kernel (csrc/optim.cu) -------------------
+    def enable_multimem(self, group=None):
+        """Re-home the hash table and its gradient into symmetric memory (torch.distributed._symmetric_memory) and
+        exchange the handles with the other ranks.  Collective; call once, before any CUDA-graph capture.  Returns
+        True when the fabric offers multicast (NVSwitch / NVLS); otherwise nothing changes and step_sharded (NCCL)
+        stays the path."""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        if self.table is None or getattr(self, "_mc", None) is not None:
+            return getattr(self, "_mc", None) is not None
+        group = group or dist.group.WORLD
+        n = self.table.numel()
+        dev = self.table.device
+        p_sym = symm_mem.empty(n, dtype=torch.float32, device=dev)
+        g_sym = symm_mem.empty(n, dtype=torch.float32, device=dev)
+        hp = symm_mem.rendezvous(p_sym, group)
+        hg = symm_mem.rendezvous(g_sym, group)
+        if not hp.multicast_ptr or not hg.multicast_ptr:
+            return False
+        with torch.no_grad():
+            p_sym.copy_(self.table.data)
+            g_sym.copy_(self.table.grad) if self.table.grad is not None else g_sym.zero_()
+        self.table.data = p_sym
+        self.table.grad = g_sym
+        self._mc = dict(p=hp, g=hg, p_sym=p_sym, g_sym=g_sym)
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=group)
+        return True
+
+    def step_multimem(self, rank, world, lr=None):
+        """Same update as step_sharded; the table's exchange and update are ONE kernel over NVLink multicast."""
+        import torch.distributed as dist
+        import ctypes
+        mc = self._mc
+        lr = self.lr if lr is None else lr
+        self.step_count += 1
+        b1, b2 = self.betas
+        stream = _lib.current_stream()
+        scale = 1.0 / world
+        small = dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, async_op=True)
+        n_active, active = self.active_prefix()
+        p = self.table
+        assert n_active % (4 * world) == 0, "active prefix must split evenly across ranks"
+        old = getattr(self, "_shard_prefix", None)
+        if old is not None and old != n_active:     # ownership is about to move: make the moments whole first
+            part = old // world
+            for buf in (self.table_m, self.table_v):
+                dist.all_gather_into_tensor(buf[:old], buf[rank * part:(rank + 1) * part].clone())
+        self._shard_prefix = n_active
+        if active > self.applied_levels:      # levels activated this step catch up on their skipped weight decay
+            lo = self.level_end[self.applied_levels - 1] if self.applied_levels > 0 else 0
+            hi = self.level_end[active - 1]
+            if self.pending_log_decay != 0.0:
+                _lib.check(_L().na_scale_inplace(ptr(p[lo:]), hi - lo, math.exp(self.pending_log_decay), stream),
+                           "na_scale_inplace")
+            self.applied_levels = active
+        part = n_active // world
+        mc["g"].barrier(channel=0)            # every rank's backward (and the decay catch-up) has finished
+        _lib.check(_L().na_adamw_step_multimem(ctypes.c_void_p(mc["g"].multicast_ptr), ctypes.c_void_p(mc["p"].multicast_ptr),
+                                               ptr(p), ptr(self.table_m), ptr(self.table_v), rank * part, part, lr, b1, b2,
+                                               self.eps, self.weight_decay, self.step_count, scale, 0, 0, stream),
+                   "na_adamw_step_multimem")
+        mc["p"].barrier(channel=1)            # every rank's slice has landed everywhere, every gradient has been read
+        self.table.grad[:n_active].zero_()
+        small.wait()
+        _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
+                                      self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
+                                      scale, 1, stream), "na_adamw_step")
         sdf_mod = getattr(self.model, "neural_sdf", None)
         if sdf_mod is not None and hasattr(sdf_mod, "invalidate_packed_weights"):
             sdf_mod.invalidate_packed_weights()

@@ -61,23 +61,3 @@ def shard_indices(n_items, rank, world):
     """Round-robin sharding `idx = rank, rank + world, ...` (DistributedSampler(shuffle=False), mesh.py:104-105),
     without the sampler's wrap-around padding."""
     return list(range(rank, n_items, world))
-
-
-def allreduce_gradients_chunked(flat_grad, table_grad_prefix, n_chunks=8, align=1024):
-    """Like allreduce_gradients, but the table prefix goes out as `n_chunks` asynchronous all-reduces and nothing
-    is waited for here.  Returns (scale, small_wait, [(lo, hi, wait_fn), ...]) for FusedAdamW.step, which
-    updates chunk i while chunk i+1 is still on the wire (the collective and the optimizer pass are both
-    HBM/NVLink streaming work of similar length on the 1.46 GB table, so pipelining them hides the shorter one)."""
-    w = world_size()
-    n = 0 if table_grad_prefix is None else table_grad_prefix.numel()
-    if w == 1:
-        return 1.0, None, ([(0, n, None)] if n else None)
-    small = dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM, async_op=True)
-    chunks = []
-    if n:
-        size = max((n // n_chunks + align - 1) // align * align, align)
-        for lo in range(0, n, size):
-            hi = min(lo + size, n)
-            h = dist.all_reduce(table_grad_prefix[lo:hi], op=dist.ReduceOp.SUM, async_op=True)
-            chunks.append((lo, hi, h.wait))
-    return 1.0 / w, small.wait, (chunks or None)

@@ -14,8 +14,14 @@ from .optim import FusedAdamW
 
 class TrainStep:
     def __init__(self, model, cfg=None, lr=1e-3, weight_decay=1e-2, max_iter=500000, warm_up_end=5000,
-                 loss_weights=None, two_steps=(300000, 400000), gamma=10.0, use_cuda_graph=False, allow_tf32=True):
+                 loss_weights=None, two_steps=(300000, 400000), gamma=10.0, use_cuda_graph=False, allow_tf32=True,
+                 data_parallel=True, table_exchange="auto"):
+        """data_parallel=False keeps this trainer local even inside an initialised process group (used to compute a
+        single-process reference trajectory).  table_exchange: "multimem" = one fused kernel over NVLink multicast,
+        "nccl" = reduce-scatter / owner AdamW / all-gather, "auto" = multimem where the fabric offers it."""
         self.model = model
+        self.data_parallel = data_parallel and parallel.world_size() > 1
+        self.table_exchange = table_exchange
         # imaginaire/trainers/base.py:169-178 (init_amp): TF32 library GEMMs are allowed by default.  Here that
         # only concerns the colour / background MLPs and the weight-gradient reductions; the SDF network, whose
         # finite differences need fp32-grade products, runs in the split-precision tcgen05 kernels regardless.
@@ -32,9 +38,16 @@ class TrainStep:
         self.c2f = sdf_cfg.encoding.type == "hashgrid" and sdf_cfg.encoding.coarse2fine.enabled
         self.numerical = sdf_cfg.gradient.mode == "numerical"
         model.neural_sdf.warm_up_end = warm_up_end          # trainer.py:32
-        parallel.broadcast_parameters([p.data for p in model.parameters()])
+        if self.data_parallel:
+            parallel.broadcast_parameters([p.data for p in model.parameters()])
         self.optim = FusedAdamW(model, lr=lr, weight_decay=weight_decay)
+        self.multimem = False
+        if self.data_parallel and self.optim.table is not None and self.optim.lazy and table_exchange in ("auto", "multimem"):
+            self.multimem = self.optim.enable_multimem()
+            if table_exchange == "multimem" and not self.multimem:
+                raise RuntimeError("table_exchange='multimem' requested but the fabric offers no multicast")
         self.current_iteration = 0
+        self.record_phases, self.phase_events = False, []
         self.losses, self.metrics = {}, {}
         # CUDA-graph mode: forward + loss + backward are captured once per schedule state and replayed; the
         # per-iteration scalars that torch ops consume (loss weights) live in a device tensor.
@@ -137,18 +150,32 @@ class TrainStep:
         self.start_of_iteration(it)
         self.model.train()
         self._upload_weights()
+        ev = None
+        if self.record_phases:     # three CUDA events per step: start / gradients ready / parameters updated
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            self.phase_events.append(ev)
+            ev[0].record()
         if self.use_cuda_graph:
             loss = self._graphed_forward_backward(data)
         else:
             loss = self._forward_backward(data)
+        if ev:
+            ev[1].record()
         lr = self.base_lr * self.lr_factor(it)
-        world = parallel.world_size()
+        world = parallel.world_size() if self.data_parallel else 1
         if world > 1 and self.optim.table is not None and self.optim.lazy:
             import torch.distributed as dist
-            self.optim.step_sharded(dist.get_rank(), world, lr=lr)     # reduce-scatter / owner update / all-gather
+            if self.multimem:
+                self.optim.step_multimem(dist.get_rank(), world, lr=lr)    # one kernel over NVLink multicast
+            else:
+                self.optim.step_sharded(dist.get_rank(), world, lr=lr)     # reduce-scatter / owner update / all-gather
+        elif world == 1:
+            self.optim.step(grad_scale=1.0, lr=lr)
         else:
             grad_scale = parallel.allreduce_gradients(*self.optim.grad_views())
             self.optim.step(grad_scale=grad_scale, lr=lr)
         self.model.neural_sdf.refresh_packed_weights()   # outside any captured graph (see NeuralSDF)
+        if ev:
+            ev[2].record()
         self.current_iteration += 1
         return loss

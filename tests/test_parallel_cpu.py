@@ -80,23 +80,3 @@ def test_block_sharding_is_round_robin_without_padding():
     # 4096 blocks (res 2048 / block 128) over 8 ranks: 512 each, block idx = rank (mod 8), as DistributedSampler(shuffle=False)
     s8 = [parallel.shard_indices(4096, r, 8) for r in range(8)]
     assert all(len(s) == 512 for s in s8) and s8[3][:3] == [3, 11, 19]
-
-
-def _chunked_case(rank, world):
-    from neuralangelo_b200 import parallel
-    flat = torch.full((10,), float(rank + 1))
-    table = torch.arange(5000, dtype=torch.float32) * (rank + 1)
-    scale, small_wait, chunks = parallel.allreduce_gradients_chunked(flat, table[:4100], n_chunks=3, align=256)
-    small_wait()
-    for lo, hi, wait in chunks:
-        wait()
-    return flat.tolist(), table.tolist(), scale, [(lo, hi) for lo, hi, _ in chunks]
-
-
-def test_chunked_gradient_allreduce_tiles_the_prefix():
-    out = _run(_chunked_case)
-    for rank, (flat, table, scale, spans) in enumerate(out):
-        assert scale == 0.5 and flat == [3.0] * 10
-        assert spans[0][0] == 0 and spans[-1][1] == 4100 and all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
-        assert table[:4100] == [i * 3.0 for i in range(4100)]
-        assert table[4100:] == [i * float(rank + 1) for i in range(4100, 5000)]
