@@ -431,7 +431,7 @@ def extra_mesh(rank, world, dev, res=2048):
     net.warm_up_end = 5000
     net.set_active_levels(500000)
     bounds = np.array([[-1.0, 1.0]] * 3)
-    fn = lambda x: -net.sdf(x)
+    fn = mesh.LatticeSDF(net)      # -sdf (scripts/extract_mesh.py:85), block queries straight from the lattice axes
     mesh.extract_mesh(fn, bounds, intv=2.0 / 128, block_res=128)   # warm-up
     if world > 1:
         torch.distributed.barrier()

@@ -115,6 +115,17 @@ int na_hashgrid_taps_bwd_strided(const na_hashgrid_desc* desc, const float* x, i
                                  uint32_t n_taps, const float* dout, int64_t point_stride, int64_t tap_stride,
                                  int64_t level_stride, float* dtable, void* stream);
 
+/* Lattice block query: the encode of the nx*ny*nz points (x slowest) of an axis-aligned lattice given by its three
+ * axis arrays (device pointers) -- one block of extract_mesh -- without materialising the [N,3] coordinates.  Features
+ * go to out[n*point_stride + l*level_stride + f]; when xyz_out is given, (x, y, z, 0) of point n is written at
+ * xyz_out + n*xyz_stride (the xyz chunk plane of na_sdf_head_fwd_planes).  8 features per level, 32-byte aligned out.
+ * Replaces: LatticeGrid.__getitem__'s meshgrid/stack + the H2D copy + the encode of
+ * projects/neuralangelo/utils/mesh.py:32-35,96-99. */
+int na_hashgrid_lattice_fwd_strided(const na_hashgrid_desc* desc, const float* table, const float* gx,
+                                    const float* gy, const float* gz, int nx, int ny, int nz, na_unit_map map,
+                                    uint32_t active_levels, float* out, int64_t point_stride, int64_t level_stride,
+                                    float* xyz_out, int64_t xyz_stride, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * NeuS volume rendering and hierarchical resampling (one warp per ray).
  * All tensors fp32 contiguous, [n_rays, n_samples(, k)].  `dist_far` is [n_rays] or NULL (= 1e10,

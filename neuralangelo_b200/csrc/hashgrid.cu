@@ -514,12 +514,20 @@ __device__ __forceinline__ void r8_store_stream(float* p, const R8& r, uint64_t 
                  : "memory");
 }
 
+// optional point source: the points of a lattice block given by its three axis arrays instead of an [N,3] array
+struct LatticeSource {
+    const float *gx, *gy, *gz;
+    int ny, nz;
+    float* xyz_out;       // optional: xyz of every point (4 floats written per point), e.g. the MLP's xyz chunk plane
+    int64_t xyz_stride;   // floats between consecutive points in xyz_out
+};
+
 template <int NT>
 __global__ void __launch_bounds__(kThreads, 2)
 hashgrid_axis_fwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ table,
                          const float* __restrict__ x, int64_t n_points, na_unit_map map, uint32_t active_levels,
                          const AxisTaps taps, float* __restrict__ out, int64_t out_stride, int64_t out_tap_stride,
-                         int64_t out_level_stride) {
+                         int64_t out_level_stride, const LatticeSource lat) {
     constexpr int F = 8;
     __shared__ LevelS sl[NA_MAX_LEVELS];
     stage_levels(desc, sl);
@@ -533,12 +541,21 @@ hashgrid_axis_fwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
         const int64_t n = cta_base + it * kThreads + threadIdx.x;
         if (n >= n_points) break;
         float* o = out + n * out_stride + level * out_level_stride;
+        float xs[3];
+        if (lat.gx) {   // point n of an axis-aligned lattice block, x slowest (mesh.py:96-99 meshgrid order): no xyz array
+            const int64_t plane = (int64_t)lat.ny * lat.nz;
+            const int i = (int)(n / plane), j = (int)((n / lat.nz) % lat.ny), k = (int)(n % lat.nz);
+            xs[0] = __ldg(lat.gx + i), xs[1] = __ldg(lat.gy + j), xs[2] = __ldg(lat.gz + k);
+            if (level == 0 && lat.xyz_out)
+                *reinterpret_cast<float4*>(lat.xyz_out + n * lat.xyz_stride) = make_float4(xs[0], xs[1], xs[2], 0.f);
+        } else {
+            xs[0] = __ldg(x + n * 3 + 0), xs[1] = __ldg(x + n * 3 + 1), xs[2] = __ldg(x + n * 3 + 2);
+        }
         if (level >= active_levels) {   // coarse-to-fine mask: inactive levels are exactly zero
 #pragma unroll
             for (int t = 0; t < NT; ++t) r8_store_stream(o + t * out_tap_stride, r8_zero(), stream);
             continue;
         }
-        const float xs[3] = {__ldg(x + n * 3 + 0), __ldg(x + n * 3 + 1), __ldg(x + n * 3 + 2)};
         const AxisCell C = axis_locate(L, map, taps, xs);
         // the eight rows of the cell, folded into the per-axis slot sums (two batches of four rows in flight)
         R8 P[3][2];
@@ -837,10 +854,12 @@ int launch_fwd(const na_hashgrid_desc* desc, const float* table, const float* x,
             dim3 g((unsigned)nb, desc->n_levels);
             if (tp.n == 1)
                 hashgrid_axis_fwd_kernel<1><<<g, kThreads, 0, stream>>>(*desc, table, x, n_points, map, active_levels, at,
-                                                                        out, out_stride, out_tap_stride, out_level_stride);
+                                                                        out, out_stride, out_tap_stride, out_level_stride,
+                                                                        LatticeSource{});
             else
                 hashgrid_axis_fwd_kernel<7><<<g, kThreads, 0, stream>>>(*desc, table, x, n_points, map, active_levels, at,
-                                                                        out, out_stride, out_tap_stride, out_level_stride);
+                                                                        out, out_stride, out_tap_stride, out_level_stride,
+                                                                        LatticeSource{});
             NA_CHECK_LAUNCH("hashgrid_axis_fwd_kernel");
             return NA_OK;
         }
@@ -1020,4 +1039,31 @@ extern "C" int na_hashgrid_bwd(const na_hashgrid_desc* desc, const float* x, int
                                void* stream) {
     const float zero[3] = {0.f, 0.f, 0.f};
     return na_hashgrid_taps_bwd(desc, x, n_points, map, active_levels, zero, 1, dout, dout_stride, 0, dtable, stream);
+}
+
+// Lattice block query: encode the (nx, ny, nz) points of an axis-aligned lattice given by its three axis arrays (device
+// pointers), x slowest -- the blocks of extract_mesh -- without materialising their [N,3] coordinates; optionally the
+// coordinates are written as the MLP's xyz chunk (4 floats per point at xyz_out + n * xyz_stride).
+extern "C" int na_hashgrid_lattice_fwd_strided(const na_hashgrid_desc* desc, const float* table, const float* gx,
+                                               const float* gy, const float* gz, int nx, int ny, int nz, na_unit_map map,
+                                               uint32_t active_levels, float* out, int64_t out_stride,
+                                               int64_t out_level_stride, float* xyz_out, int64_t xyz_stride,
+                                               void* stream) {
+    na::clear_error();
+    const int64_t n_points = (int64_t)nx * ny * nz;
+    if (int rc = validate(desc, table, gx, n_points, active_levels)) return rc;
+    NA_REQUIRE(nx > 0 && ny > 0 && nz > 0 && gy != nullptr && gz != nullptr && out != nullptr, "lattice fwd: bad arguments");
+    NA_REQUIRE(desc->n_features == 8, "lattice fwd: 8 features per level only");
+    NA_REQUIRE(row_aligned(out, out_stride, 8, out_level_stride) && row_aligned(table, 8, 8, 8),
+               "lattice fwd: out / table must be 32-byte aligned with strides that are multiples of 8 floats");
+    NA_REQUIRE(xyz_out == nullptr || ((uintptr_t)xyz_out % 16 == 0 && xyz_stride % 4 == 0 && xyz_stride >= 4),
+               "lattice fwd: xyz_out must be 16-byte aligned with a stride that is a multiple of 4 floats");
+    AxisTaps at{};
+    LatticeSource lat{gx, gy, gz, ny, nz, xyz_out, xyz_stride};
+    const int64_t nb = (n_points + kAxisPoints - 1) / kAxisPoints;
+    dim3 g((unsigned)nb, desc->n_levels);
+    hashgrid_axis_fwd_kernel<1><<<g, kThreads, 0, (cudaStream_t)stream>>>(*desc, table, nullptr, n_points, map, active_levels, at,
+                                                                           out, out_stride, 0, out_level_stride, lat);
+    NA_CHECK_LAUNCH("hashgrid_axis_fwd_kernel (lattice)");
+    return NA_OK;
 }

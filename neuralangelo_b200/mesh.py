@@ -26,22 +26,28 @@ from ._lib import ptr
 _L = _lib.lib
 
 
-def mc(volume, isovalue=0.0, scale=1.0, origin=None):
-    """`mcubes.marching_cubes(volume, isovalue)` on a CUDA float32 tensor [X,Y,Z].
-    Returns (vertices float64 [nV,3], triangles int64 [nF,3]) on the same device; vertex and face
-    order are those of the serial algorithm.  vertices = index position * scale + origin (mesh.py:123)."""
-    _lib.require_cuda(volume)
-    vol = _lib.f32c(volume)
-    nx, ny, nz = vol.shape
-    dev = vol.device
+def _mc_scratch(nx, ny, nz, dev):
     nbytes = _L().na_mc_scratch_bytes(nx, ny, nz)
     scratch = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
     base = (scratch.data_ptr() + 255) // 256 * 256
-    sptr = ctypes.c_void_p(base)
-    counts = torch.empty(2, dtype=torch.int32, device=dev)
-    stream = _lib.current_stream()
-    _lib.check(_L().na_mc_count(ptr(vol), nx, ny, nz, float(isovalue), sptr, nbytes, ptr(counts), stream), "na_mc_count")
-    n_v, n_f = (int(c) for c in counts.cpu())
+    return scratch, ctypes.c_void_p(base), nbytes
+
+
+def mc_count(vol, isovalue, counts_slot):
+    """First half of marching cubes (classify + scan): fills `counts_slot` (int32 [2] device view: vertices, faces) and
+    returns the scratch the emission needs.  No host synchronisation."""
+    nx, ny, nz = vol.shape
+    scratch, sptr, nbytes = _mc_scratch(nx, ny, nz, vol.device)
+    _lib.check(_L().na_mc_count(ptr(vol), nx, ny, nz, float(isovalue), sptr, nbytes, ptr(counts_slot), _lib.current_stream()),
+               "na_mc_count")
+    return scratch, sptr, nbytes
+
+
+def mc_emit(vol, isovalue, scratch_info, n_v, n_f, scale=1.0, origin=None):
+    """Second half: vertices float64 [n_v,3] and triangles int32 [n_f,3] for counts already known on the host."""
+    nx, ny, nz = vol.shape
+    _, sptr, nbytes = scratch_info
+    dev = vol.device
     verts = torch.empty(n_v, 3, dtype=torch.float64, device=dev)
     faces = torch.empty(n_f, 3, dtype=torch.int32, device=dev)
     if n_v or n_f:
@@ -49,9 +55,37 @@ def mc(volume, isovalue=0.0, scale=1.0, origin=None):
         if origin is not None:
             org = (ctypes.c_double * 3)(*[float(o) for o in origin])
         _lib.check(_L().na_mc_emit(ptr(vol), nx, ny, nz, float(isovalue), sptr, nbytes, float(scale), org,
-                                   ptr(verts) if n_v else None, n_v, ptr(faces) if n_f else None, n_f, stream),
+                                   ptr(verts) if n_v else None, n_v, ptr(faces) if n_f else None, n_f, _lib.current_stream()),
                    "na_mc_emit")
+    return verts, faces
+
+
+def mc(volume, isovalue=0.0, scale=1.0, origin=None):
+    """`mcubes.marching_cubes(volume, isovalue)` on a CUDA float32 tensor [X,Y,Z].
+    Returns (vertices float64 [nV,3], triangles int64 [nF,3]) on the same device; vertex and face
+    order are those of the serial algorithm.  vertices = index position * scale + origin (mesh.py:123)."""
+    _lib.require_cuda(volume)
+    vol = _lib.f32c(volume)
+    counts = torch.empty(2, dtype=torch.int32, device=vol.device)
+    info = mc_count(vol, isovalue, counts)
+    n_v, n_f = (int(c) for c in counts.cpu())
+    verts, faces = mc_emit(vol, isovalue, info, n_v, n_f, scale=scale, origin=origin)
     return verts, faces.long()
+
+
+class LatticeSDF:
+    """`sdf_func` for extract_mesh that also knows how to query a whole lattice block from its axis arrays
+    (NeuralSDF.sdf_lattice): extract_mesh then never materialises block coordinates.  `sign=-1` is the flip
+    scripts/extract_mesh.py:85 applies (`lambda x: -neural_sdf.sdf(x)`)."""
+
+    def __init__(self, neural_sdf, sign=-1.0):
+        self.neural_sdf, self.sign = neural_sdf, float(sign)
+
+    def __call__(self, xyz):
+        return self.sign * self.neural_sdf.sdf(xyz)
+
+    def lattice(self, gx, gy, gz):
+        return self.sign * self.neural_sdf.sdf_lattice(gx, gy, gz)
 
 
 class Mesh:
@@ -263,7 +297,50 @@ def extract_mesh(sdf_func, bounds, intv, block_res=64, texture_func=None, filter
     v_parts, f_parts, c_parts, v_total = [], [], [], 0
     import time
     t_start = time.perf_counter()
-    for idx in range(rank, len(grid), world):
+    my_blocks = list(range(rank, len(grid), world))
+    if texture_func is None and not filter_lcc:
+        # Fast path: no per-block host round trip.  The lattice axes live on the device once; blocks are queried
+        # (from their axes when sdf_func offers `.lattice`, else from a device-built coordinate block) and classified
+        # in batches of `batch` blocks, ONE read-back of the batch's (vertex, face) counts sizes the outputs, and the
+        # bounding-sphere filter (mesh.py:136-148) runs once over the concatenated result -- removing out-of-sphere
+        # vertices block by block or all at once keeps the same vertices and faces in the same order.
+        axes_dev = [g.to(device) for g in (grid.x_grid, grid.y_grid, grid.z_grid)]
+        axes_host = [g.double().tolist() for g in (grid.x_grid, grid.y_grid, grid.z_grid)]
+        r, batch = grid.block_res, 16
+        lattice_query = getattr(sdf_func, "lattice", None)
+        for b0 in range(0, len(my_blocks), batch):
+            chunk = my_blocks[b0:b0 + batch]
+            counts = torch.zeros(len(chunk), 2, dtype=torch.int32, device=device)
+            pending = []
+            for k, idx in enumerate(chunk):
+                bx, by, bz = idx // (grid.num_blocks_y * grid.num_blocks_z), (idx // grid.num_blocks_z) % grid.num_blocks_y, \
+                    idx % grid.num_blocks_z
+                gx, gy, gz = axes_dev[0][bx * r:bx * r + r + 1], axes_dev[1][by * r:by * r + r + 1], \
+                    axes_dev[2][bz * r:bz * r + r + 1]
+                if min(gx.numel(), gy.numel(), gz.numel()) < 2:
+                    continue            # a one-sample-thick remainder block has no cells
+                if lattice_query is not None:
+                    sdf = lattice_query(gx, gy, gz)
+                else:
+                    sdf = sdf_func(torch.stack(torch.meshgrid(gx, gy, gz, indexing="ij"), dim=-1))[..., 0]
+                sdf = _lib.f32c(sdf)
+                origin = (axes_host[0][bx * r], axes_host[1][by * r], axes_host[2][bz * r])
+                pending.append((k, sdf, mc_count(sdf, 0.0, counts[k]), origin))
+            counts_host = counts.cpu().tolist()          # the only synchronisation of the batch
+            for k, sdf, info, origin in pending:
+                n_v, n_f = counts_host[k]
+                if n_v == 0:
+                    continue
+                Vb, Fb = mc_emit(sdf, 0.0, info, n_v, n_f, scale=float(intv), origin=origin)
+                v_parts.append(Vb)
+                f_parts.append(Fb.long() + v_total)
+                v_total += n_v
+        V = torch.cat(v_parts) if v_parts else torch.zeros(0, 3, dtype=torch.float64, device=device)
+        F = torch.cat(f_parts) if f_parts else torch.zeros(0, 3, dtype=torch.long, device=device)
+        if V.shape[0] > 0:
+            V, F, _ = filter_points_outside_bounding_sphere(V, F, None)
+        v_parts, f_parts, my_blocks = [V], [F], []
+    for idx in my_blocks:
         gx, gy, gz = (g.to(device) for g in grid.block_axes(idx))
         xyz = torch.stack(torch.meshgrid(gx, gy, gz, indexing="ij"), dim=-1)
         sdf = sdf_func(xyz)[..., 0]

@@ -161,6 +161,24 @@ class NeuralSDF(torch.nn.Module):
         sdf = self._packed_mlp().forward_planes(planes, planes.shape[1])
         return sdf.view(len(taps), points_flat.shape[0], 1)
 
+    def sdf_lattice(self, gx, gy, gz):
+        """SDF on the lattice gx x gy x gz (float32 CUDA axis arrays, x slowest: one block of extract_mesh) without an
+        [N,3] coordinate tensor: the encode kernel derives each point from the axes and writes the MLP's xyz chunk
+        itself (na_hashgrid_lattice_fwd_strided), then one launch of the pipelined SDF-only MLP.  Returns [nx,ny,nz]."""
+        import ctypes
+        enc = self.tcnn_encoding
+        if not self._planes_supported():
+            raise NotImplementedError("sdf_lattice needs the chunk-plane path (8 features per level, fused MLP envelope)")
+        nx, ny, nz = gx.numel(), gy.numel(), gz.numel()
+        n, n_levels = nx * ny * nz, enc.desc.n_levels
+        planes = torch.empty(n_levels + 1, n, 8, dtype=torch.float32, device=gx.device)
+        rc = _lib.lib().na_hashgrid_lattice_fwd_strided(
+            ctypes.byref(enc.desc), _lib.ptr(enc.params.detach()), _lib.ptr(gx), _lib.ptr(gy), _lib.ptr(gz), nx, ny, nz,
+            self._unit_map, int(self._levels_in_use()), _lib.ptr(planes), 8, n * 8, _lib.ptr(planes[n_levels]), 8,
+            _lib.current_stream())
+        _lib.check(rc, "na_hashgrid_lattice_fwd_strided")
+        return self._packed_mlp().forward_planes(planes, n).view(nx, ny, nz)
+
     def _needs_graph(self):
         return torch.is_grad_enabled() and (self.tcnn_encoding.params.requires_grad
                                             or any(p.requires_grad for p in self.mlp.parameters()))

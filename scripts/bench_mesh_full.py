@@ -15,7 +15,7 @@ net = NeuralSDF(default_model_config().object.sdf).to(dev).eval()
 net.warm_up_end = 5000
 net.set_active_levels(500000)
 bounds = np.array([[-1.0, 1.0]] * 3)
-fn = lambda x: -net.sdf(x)
+fn = mesh.LatticeSDF(net)   # block queries straight from the lattice axes (no xyz tensor)
 mesh.extract_mesh(fn, bounds, intv=2.0 / 128, block_res=128)
 if world > 1: dist.barrier()
 torch.cuda.synchronize(); t0 = time.perf_counter()

@@ -379,3 +379,37 @@ def test_default_config_matches_reference(na_lib, cuda_device, golden_dir, taps,
     assert rel <= 2e-2 + 4 * float(G["tg_sens_rel"][:active].max()), rel
     zidx = torch.from_numpy(G["tg_zero_index"]).to(d)
     assert float(tg[zidx].abs().max()) == 0.0
+
+
+def test_lattice_query_and_batched_extraction_match_the_coordinate_path(na_lib, cuda_device):
+    """NeuralSDF.sdf_lattice (axes in, no [N,3] tensor: na_hashgrid_lattice_fwd_strided) is bit-identical to querying the
+    materialised meshgrid, and extract_mesh's batched no-round-trip path returns the same mesh whether sdf_func offers
+    `.lattice` or is a plain callable (mesh.py:24-49, 96-99)."""
+    from neuralangelo_b200 import mesh
+    from neuralangelo_b200.config import default_model_config
+    from neuralangelo_b200.modules import NeuralSDF
+    torch.manual_seed(5)
+    cfg = default_model_config()
+    net = NeuralSDF(cfg.object.sdf).to(cuda_device).eval()
+    with torch.no_grad():
+        net.tcnn_encoding.params.uniform_(-0.05, 0.05)
+        for lin in net.mlp.linears:
+            lin.weight_v.add_(torch.randn_like(lin.weight_v) * 0.02)
+    net.warm_up_end = 0
+    net.set_active_levels(current_iter=11 * cfg.object.sdf.encoding.coarse2fine.step)   # 11 of 16 levels
+    gx = torch.linspace(-0.9, 0.7, 37, device=cuda_device)
+    gy = torch.linspace(-0.5, 0.8, 21, device=cuda_device)
+    gz = torch.linspace(-1.0, 1.0, 45, device=cuda_device)
+    with torch.no_grad():
+        lat = net.sdf_lattice(gx, gy, gz)
+        ref = net.sdf(torch.stack(torch.meshgrid(gx, gy, gz, indexing="ij"), dim=-1))[..., 0]
+    assert lat.shape == (37, 21, 45) and torch.equal(lat, ref)
+    bounds = np.array([[-1.0, 1.0]] * 3)
+    a = mesh.extract_mesh(mesh.LatticeSDF(net), bounds, intv=2.0 / 80, block_res=32)
+    b = mesh.extract_mesh(lambda x: -net.sdf(x), bounds, intv=2.0 / 80, block_res=32)
+    assert len(a.vertices) > 1000 and np.array_equal(a.vertices, b.vertices) and np.array_equal(a.faces, b.faces)
+    assert np.linalg.norm(a.vertices, axis=1).max() < 1.0
+    # against the per-block path (texture_func forces it; colours ignored)
+    c = mesh.extract_mesh(lambda x: -net.sdf(x), bounds, intv=2.0 / 80, block_res=32,
+                          texture_func=lambda xyz: np.zeros((len(xyz), 3), dtype=np.uint8))
+    assert np.array_equal(a.vertices, c.vertices) and np.array_equal(a.faces, c.faces)
