@@ -12,6 +12,7 @@
 // transmittance product is a reverse affine scan (no division by 1-alpha, which the clip to [0,1]
 // at model.py:290 makes exactly zero in practice).
 #include "na_common.cuh"
+#include "tc_common.cuh"
 #include <math.h>
 
 namespace {
@@ -19,7 +20,14 @@ namespace {
 constexpr int kWarpsPerCta = 8;
 constexpr unsigned kFull = 0xffffffffu;
 
-__device__ __forceinline__ float sigmoidf(float x) { return 1.f / (1.f + expf(-x)); }
+// ex2.approx / rcp.approx forms: with the rows staged in shared memory the renderer is bound by instruction issue, and
+// the IEEE expf / division sequences were a third of its instructions.  Relative error ~1e-6 (argument rounding of
+// x * log2(e) for |x| up to ~60), against the 2e-5 tolerance of the parity tests.
+__device__ __forceinline__ float fast_exp(float x) { return __expf(x); }
+__device__ __forceinline__ float sigmoidf(float x) { return __fdividef(1.f, 1.f + fast_exp(-x)); }
+// IEEE form for the hierarchical sampler: its inverse-CDF step is ill-conditioned where the CDF is flat, so it keeps the
+// reference's arithmetic to the last bit it can
+__device__ __forceinline__ float sigmoid_ieee(float x) { return 1.f / (1.f + expf(-x)); }
 
 // Inclusive product scan over the warp's lanes.
 __device__ __forceinline__ float warp_scan_prod(float v, int lane) {
@@ -95,12 +103,13 @@ __device__ __forceinline__ NeusAlpha neus_alpha(float sdf, float true_cos, float
     const float est_prev = sdf - half, est_next = sdf + half;
     const float p = sigmoidf(est_prev * inv_s), q = sigmoidf(est_next * inv_s);
     const float denom = p + 1e-5f;
-    const float raw = (p - q) / denom;
+    const float raw = __fdividef(p - q, denom);
     NeusAlpha r;
     r.alpha = fminf(fmaxf(raw, 0.f), 1.f);
     if (WITH_GRAD) {
         const bool pass = (raw >= 0.f) && (raw <= 1.f);  // clamp backward is inclusive at the bounds
-        const float da_dp = (q + 1e-5f) / (denom * denom), da_dq = -1.f / denom;
+        const float rden = __fdividef(1.f, denom);
+        const float da_dp = (q + 1e-5f) * rden * rden, da_dq = -rden;
         const float gp = pass ? da_dp * p * (1.f - p) : 0.f;  // d alpha / d (est_prev*inv_s)
         const float gq = pass ? da_dq * q * (1.f - q) : 0.f;
         r.d_sdf = (gp + gq) * inv_s;
@@ -332,7 +341,7 @@ neus_upsample_kernel(const float* __restrict__ dists, const float* __restrict__ 
             const float prev = i > 0 ? (s0 - s[i - 1]) / (d0 - d[i - 1] + 1e-5f) : 0.f;
             cosv = fminf(prev, cosv);
             const float half = cosv * (d1 - d0) * 0.5f;
-            const float p = sigmoidf((mid - half) * inv_s), q = sigmoidf((mid + half) * inv_s);
+            const float p = sigmoid_ieee((mid - half) * inv_s), q = sigmoid_ieee((mid + half) * inv_s);
             alpha = fminf(fmaxf((p - q) / (p + 1e-5f), 0.f), 1.f);
         }
         const float T = transmittance_chunk(alpha, lane, carry);
@@ -427,7 +436,7 @@ neus_render_kernel(const RenderArgs A, float* __restrict__ rgb_out, float* __res
         } else if (i < n) {
             const int ib = i - n_obj;
             const float dt = interval(dbg, ib, n_bg, 1e10f);
-            const float e = expf(-A.dens_bg[ray * n_bg + ib] * dt);
+            const float e = fast_exp(-A.dens_bg[ray * n_bg + ib] * dt);
             al = 1.f - e;
             gsdf[c] = dt * e;
         }
@@ -487,6 +496,198 @@ neus_render_kernel(const RenderArgs A, float* __restrict__ rgb_out, float* __res
     }
     ds_acc = warp_sum(ds_acc) * inv_s;
     if (lane == 0 && ds_acc != 0.f) atomicAdd(d_s_var, ds_acc);
+}
+
+// ------------------------------------------------------------------------------------------
+// The same renderer with every ray's rows STAGED IN SHARED MEMORY by bulk asynchronous copies (cp.async.bulk,
+// mbarrier completion): the direct kernel above reads nine lane-strided 4-byte streams per warp (gradient and colour
+// rows at a 12-byte lane stride) and reached 0.48 / 0.39 of the HBM peak (profiles/r01_render_ncu_summary.md: DRAM 43 %
+// busy, long_scoreboard).  Here one lane requests the ray's rows as a handful of contiguous bulk copies, the next
+// ray's rows are in flight while the current ray is scanned (two buffers per warp), the per-sample gradients of the
+// backward are collected in shared memory as well and leave as bulk stores.  Persistent CTAs; a warp owns rays
+// warp_id, warp_id + total_warps, ...  Applies when every row is a multiple of 16 bytes (samples % 4 == 0) and the
+// tensors are 16-byte aligned; the direct kernel remains for everything else.
+// ------------------------------------------------------------------------------------------
+struct StagedLayout {   // float offsets inside one warp's input buffer / output buffer
+    int sdf, grad, dob, rgb, dens, dbg, rgbb, dw, in_floats;
+    int o_sdf, o_grad, o_rgb, o_dens, o_rgbb, out_floats;
+};
+
+__host__ __device__ inline StagedLayout staged_layout(int n_obj, int n_bg, bool bwd, bool with_dw) {
+    StagedLayout L;
+    int o = 0;
+    L.sdf = o, o += n_obj;
+    L.grad = o, o += 3 * n_obj;
+    L.dob = o, o += n_obj;
+    L.rgb = o, o += 3 * n_obj;
+    L.dens = o, o += n_bg;
+    L.dbg = o, o += n_bg;
+    L.rgbb = o, o += 3 * n_bg;
+    L.dw = o, o += (bwd && with_dw) ? n_obj + n_bg : 0;
+    L.in_floats = o;
+    // the backward's per-sample gradients overwrite the rows they are the gradients of (same lane, read before write)
+    L.o_sdf = L.sdf, L.o_grad = L.grad, L.o_rgb = L.rgb, L.o_dens = L.dens, L.o_rgbb = L.rgbb;
+    L.out_floats = 0;
+    return L;
+}
+
+__device__ __forceinline__ void bulk_store_s2g(void* dst, uint32_t src_smem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes)
+                 : "memory");
+}
+
+template <int MAXC, bool BWD>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+neus_render_staged_kernel(const RenderArgs A, float* __restrict__ rgb_out, float* __restrict__ weights_out,
+                          float* __restrict__ opacity_out, const float* __restrict__ d_rgb,
+                          const float* __restrict__ d_weights, float* __restrict__ d_sdf, float* __restrict__ d_grad,
+                          float* __restrict__ d_s_var, float* __restrict__ d_rgb_obj, float* __restrict__ d_dens_bg,
+                          float* __restrict__ d_rgb_bg) {
+    using namespace na_tc;
+    extern __shared__ __align__(128) float smem_f[];
+    __shared__ uint64_t bars[kWarpsPerCta][2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n_obj = A.n_obj, n_bg = A.n_bg, n = n_obj + n_bg;
+    const StagedLayout L = staged_layout(n_obj, n_bg, BWD, d_weights != nullptr);
+    float* in_buf[2] = {smem_f + (size_t)warp * (2 * L.in_floats + L.out_floats),
+                        smem_f + (size_t)warp * (2 * L.in_floats + L.out_floats) + L.in_floats};
+    const uint32_t bar[2] = {smem_u32(&bars[warp][0]), smem_u32(&bars[warp][1])};
+    if (lane == 0) {
+        mbar_init(bar[0], 1);
+        mbar_init(bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    const float inv_s = expf(__ldg(A.s_var));
+    const float anneal = __ldg(A.anneal_ratio);
+    const int64_t warp_stride = (int64_t)gridDim.x * kWarpsPerCta;
+    const int64_t first = (int64_t)blockIdx.x * kWarpsPerCta + warp;
+
+    auto request = [&](int64_t ray, int b) {   // lane 0: all rows of `ray` -> buffer b
+        if (lane != 0 || ray >= A.n_rays) return;
+        const uint32_t bytes = (uint32_t)L.in_floats * 4u;
+        mbar_expect_tx(bar[b], bytes);
+        const uint32_t base = smem_u32(in_buf[b]);
+        bulk_copy_g2s(base + L.sdf * 4, A.sdf + ray * n_obj, n_obj * 4, bar[b]);
+        bulk_copy_g2s(base + L.grad * 4, A.grad + ray * n_obj * 3, n_obj * 12, bar[b]);
+        bulk_copy_g2s(base + L.dob * 4, A.dists_obj + ray * n_obj, n_obj * 4, bar[b]);
+        bulk_copy_g2s(base + L.rgb * 4, A.rgb_obj + ray * n_obj * 3, n_obj * 12, bar[b]);
+        if (n_bg) {
+            bulk_copy_g2s(base + L.dens * 4, A.dens_bg + ray * n_bg, n_bg * 4, bar[b]);
+            bulk_copy_g2s(base + L.dbg * 4, A.dists_bg + ray * n_bg, n_bg * 4, bar[b]);
+            bulk_copy_g2s(base + L.rgbb * 4, A.rgb_bg + ray * n_bg * 3, n_bg * 12, bar[b]);
+        }
+        if (BWD && d_weights) bulk_copy_g2s(base + L.dw * 4, d_weights + ray * n, n * 4, bar[b]);
+    };
+
+    request(first, 0);
+    uint32_t it = 0;
+    float ds_total = 0.f;
+    for (int64_t ray = first; ray < A.n_rays; ray += warp_stride, ++it) {
+        const int b = it & 1;
+        // the other buffer was consumed one iteration ago; in the backward its bulk stores must have read it out too
+        if (BWD && lane == 0 && it > 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        request(ray + warp_stride, b ^ 1);
+        const float far = A.dist_far ? __ldg(A.dist_far + ray) : 1e10f;
+        const float r0 = __ldg(A.ray_unit + ray * 3 + 0), r1 = __ldg(A.ray_unit + ray * 3 + 1),
+                    r2 = __ldg(A.ray_unit + ray * 3 + 2);
+        mbar_wait(bar[b], (it >> 1) & 1);
+        float* S = in_buf[b];
+        float* out_buf = S;
+        const float* dob = S + L.dob;
+        const float* dbg = S + L.dbg;
+        float alpha[MAXC], T[MAXC];
+        float gsdf[MAXC], gcos[MAXC], ginv[MAXC];
+        float carry = 1.f;
+        float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, accw = 0.f;
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) {
+            const int i = c * 32 + lane;
+            float al = 0.f;
+            gsdf[c] = gcos[c] = ginv[c] = 0.f;
+            if (i < n_obj) {
+                const float* gr = S + L.grad + i * 3;
+                const float tc = r0 * gr[0] + r1 * gr[1] + r2 * gr[2];
+                const NeusAlpha na_ = neus_alpha<BWD>(S[L.sdf + i], tc, interval(dob, i, n_obj, far), inv_s, anneal);
+                al = na_.alpha;
+                gsdf[c] = na_.d_sdf, gcos[c] = na_.d_cos, ginv[c] = na_.d_invs;
+            } else if (i < n) {
+                const int ib = i - n_obj;
+                const float dt = interval(dbg, ib, n_bg, 1e10f);
+                const float e = fast_exp(-S[L.dens + ib] * dt);
+                al = 1.f - e;
+                gsdf[c] = dt * e;
+            }
+            alpha[c] = al;
+            T[c] = (c * 32 < n) ? transmittance_chunk(al, lane, carry) : 0.f;
+            if (!BWD && i < n) {
+                const float w = al * T[c];
+                const float* col = i < n_obj ? S + L.rgb + i * 3 : S + L.rgbb + (i - n_obj) * 3;
+                acc0 = fmaf(w, col[0], acc0), acc1 = fmaf(w, col[1], acc1), acc2 = fmaf(w, col[2], acc2);
+                accw += w;
+                if (weights_out) weights_out[ray * n + i] = w;
+            }
+        }
+        if (!BWD) {
+            acc0 = warp_sum(acc0), acc1 = warp_sum(acc1), acc2 = warp_sum(acc2), accw = warp_sum(accw);
+            if (lane == 0) {
+                rgb_out[ray * 3 + 0] = acc0, rgb_out[ray * 3 + 1] = acc1, rgb_out[ray * 3 + 2] = acc2;
+                if (opacity_out) opacity_out[ray] = accw;
+            }
+            __syncwarp();
+            continue;
+        }
+        // ---- backward ----
+        const float g0 = __ldg(d_rgb + ray * 3 + 0), g1 = __ldg(d_rgb + ray * 3 + 1), g2 = __ldg(d_rgb + ray * 3 + 2);
+        float q = 0.f, ds_acc = 0.f;
+#pragma unroll
+        for (int c = MAXC - 1; c >= 0; --c) {
+            if (c * 32 >= n) continue;  // warp-uniform
+            const int i = c * 32 + lane;
+            float dw = 0.f;
+            if (i < n) {
+                const bool obj = i < n_obj;
+                const float* col = obj ? S + L.rgb + i * 3 : S + L.rgbb + (i - n_obj) * 3;
+                dw = g0 * col[0] + g1 * col[1] + g2 * col[2];
+                if (d_weights) dw += S[L.dw + i];
+                const float w = alpha[c] * T[c];
+                float* dcol = obj ? out_buf + L.o_rgb + i * 3 : out_buf + L.o_rgbb + (i - n_obj) * 3;
+                dcol[0] = g0 * w, dcol[1] = g1 * w, dcol[2] = g2 * w;
+            }
+            const float qi = adjoint_chunk(alpha[c], dw, lane, q);
+            if (i < n) {
+                const float da = T[c] * (dw - qi);
+                if (i < n_obj) {
+                    out_buf[L.o_sdf + i] = da * gsdf[c];
+                    const float gc = da * gcos[c];
+                    float* dg = out_buf + L.o_grad + i * 3;
+                    dg[0] = gc * r0, dg[1] = gc * r1, dg[2] = gc * r2;
+                    ds_acc = fmaf(da, ginv[c], ds_acc);
+                } else {
+                    out_buf[L.o_dens + (i - n_obj)] = da * gsdf[c];
+                }
+            }
+        }
+        ds_total += ds_acc;
+        fence_proxy_async();        // this lane's shared-memory writes become visible to the bulk-copy engine
+        __syncwarp();
+        if (lane == 0) {
+            const uint32_t ob = smem_u32(out_buf);
+            bulk_store_s2g(d_sdf + ray * n_obj, ob + L.o_sdf * 4, n_obj * 4);
+            bulk_store_s2g(d_grad + ray * n_obj * 3, ob + L.o_grad * 4, n_obj * 12);
+            bulk_store_s2g(d_rgb_obj + ray * n_obj * 3, ob + L.o_rgb * 4, n_obj * 12);
+            if (n_bg) {
+                bulk_store_s2g(d_dens_bg + ray * n_bg, ob + L.o_dens * 4, n_bg * 4);
+                bulk_store_s2g(d_rgb_bg + ray * n_bg * 3, ob + L.o_rgbb * 4, n_bg * 12);
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+    }
+    if (BWD) {
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        ds_total = warp_sum(ds_total) * inv_s;
+        if (lane == 0 && ds_total != 0.f) atomicAdd(d_s_var, ds_total);
+    }
 }
 
 inline unsigned ray_blocks(int64_t n_rays) { return (unsigned)((n_rays + kWarpsPerCta - 1) / kWarpsPerCta); }
@@ -633,6 +834,39 @@ int launch_render(const RenderArgs& A, float* rgb, float* weights, float* opacit
                   const float* d_weights, float* d_sdf, float* d_grad, float* d_s_var, float* d_rgb_obj,
                   float* d_dens_bg, float* d_rgb_bg, cudaStream_t s) {
     const int n = A.n_obj + A.n_bg;
+    {   // staged form: every row a multiple of 16 bytes at 16-byte aligned addresses, enough rays to fill the GPU
+        auto al16 = [](const void* p) { return p == nullptr || (uintptr_t)p % 16 == 0; };
+        const bool rows_ok = A.n_obj % 4 == 0 && A.n_bg % 4 == 0 && n <= 256;
+        const bool ptrs_ok = al16(A.sdf) && al16(A.grad) && al16(A.dists_obj) && al16(A.rgb_obj) && al16(A.dens_bg) &&
+                             al16(A.dists_bg) && al16(A.rgb_bg) && al16(d_weights) && al16(d_sdf) && al16(d_grad) &&
+                             al16(d_rgb_obj) && al16(d_dens_bg) && al16(d_rgb_bg);
+        const StagedLayout L = staged_layout(A.n_obj, A.n_bg, BWD, d_weights != nullptr);
+        const size_t smem = (size_t)kWarpsPerCta * (2 * L.in_floats + L.out_floats) * sizeof(float);
+        if (rows_ok && ptrs_ok && smem <= 200 * 1024 && A.n_rays >= 4096) {
+            int per_sm = (int)((220 * 1024) / (smem + 1024));
+            if (per_sm > 4) per_sm = 4;
+            if (per_sm < 1) per_sm = 1;
+            int64_t grid = (int64_t)na::kNumSMs * per_sm;
+            const int64_t need = (A.n_rays + kWarpsPerCta - 1) / kWarpsPerCta;
+            if (grid > need) grid = need;
+#define NA_RENDER_STAGED(MAXC)                                                                                        \
+    do {                                                                                                              \
+        auto kern = neus_render_staged_kernel<MAXC, BWD>;                                                             \
+        if (int rc = na::check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), \
+                                    "neus_render_staged smem"))                                                       \
+            return rc;                                                                                                \
+        kern<<<(unsigned)grid, kWarpsPerCta * 32, smem, s>>>(A, rgb, weights, opacity, d_rgb, d_weights, d_sdf, d_grad, \
+                                                             d_s_var, d_rgb_obj, d_dens_bg, d_rgb_bg);                \
+    } while (0)
+            if (n <= 64) NA_RENDER_STAGED(2);
+            else if (n <= 128) NA_RENDER_STAGED(4);
+            else if (n <= 192) NA_RENDER_STAGED(6);
+            else NA_RENDER_STAGED(8);
+#undef NA_RENDER_STAGED
+            NA_CHECK_LAUNCH("neus_render_staged_kernel");
+            return NA_OK;
+        }
+    }
     const unsigned blocks = ray_blocks(A.n_rays);
 #define NA_RENDER(MAXC)                                                                                           \
     neus_render_kernel<MAXC, BWD><<<blocks, kWarpsPerCta * 32, 0, s>>>(A, rgb, weights, opacity, d_rgb, d_weights, \

@@ -80,7 +80,10 @@ def test_golden_backward_through_pieces_and_fused(G, na_lib, cuda_device):
         torch.testing.assert_close(s_var.grad.cpu(), G["bw_d_svar"], rtol=2e-4, atol=2e-5)
 
 
-@pytest.mark.parametrize("R,N,NB", [(257, 128, 32), (64, 37, 0), (33, 300, 17), (5, 1, 1)])
+# >= 4096 rays with sample counts that are multiples of 4 take the shared-memory-staged kernel (bulk copies), the
+# rest the direct one
+@pytest.mark.parametrize("R,N,NB", [(257, 128, 32), (64, 37, 0), (33, 300, 17), (5, 1, 1), (4133, 128, 32), (4100, 64, 0),
+                                    (4101, 36, 12), (4097, 200, 56)])
 def test_fused_render_vs_oracle(na_lib, cuda_device, R, N, NB):
     from neuralangelo_b200 import render
     ray, dists, sdf, grad, far, rgb, dens, dbg, rgbb, tgt = _scene(R, N, max(NB, 1), seed=R)
@@ -113,12 +116,12 @@ def test_fused_render_vs_oracle(na_lib, cuda_device, R, N, NB):
     assert abs(sk.grad.item() - so.grad.item()) <= 2e-4 * abs(so.grad.item()) + 1e-6
 
 
-@pytest.mark.parametrize("want_weights", [True, False])
-def test_white_background_gradient_through_opacity(na_lib, cuda_device, want_weights):
+@pytest.mark.parametrize("want_weights,R", [(True, 97), (False, 97), (True, 4099)])
+def test_white_background_gradient_through_opacity(na_lib, cuda_device, want_weights, R):
     """model.py:138-140 with background.white: rgb + (1 - opacity_all) back-propagates through the opacity
     (= sum of the compositing weights).  Oracle: float64 autograd of oracle/render_ref.py."""
     from neuralangelo_b200 import render
-    R, N, NB = 97, 64, 16
+    N, NB = 64, 16
     ray, dists, sdf, grad, far, rgb, dens, dbg, rgbb, tgt = _scene(R, N, NB, seed=11)
     s = torch.tensor(2.5)
     leaf = lambda t: t.clone().requires_grad_(True)
