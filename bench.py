@@ -547,8 +547,16 @@ def extra_composite(dev, log2_rays=20):
     d_rgb = torch.randn_like(out)
     ms_b = timed(lambda: torch.autograd.grad(out, [sdf, grad, rgb, dens, rgbb, s_var], d_rgb, retain_graph=True))
     by_b = R * (b_in + 12 + N * 28 + NB * 16)  # inputs re-read + d_rgb; d_sdf, d_grad, d_rgb, d_dens, d_rgb_bg written
+    kw_w = dict(kw, want_weights=True)
+
+    def fwd_w():
+        with torch.no_grad():
+            render.neus_render(ray, sdf, grad, dists, s_var, rgb, **kw_w)
+    ms_fw = timed(fwd_w)
+    by_fw = by_f + R * (N + NB) * 4     # + the compositing weights the training step keeps (model.py:141)
     return {"rays": R, "samples": [N, NB],
             "fwd": {"ms": ms_f, "GBps": by_f / ms_f / 1e6, "frac_of_hbm_peak": by_f / ms_f / 1e6 / peak},
+            "fwd_with_weights": {"ms": ms_fw, "GBps": by_fw / ms_fw / 1e6, "frac_of_hbm_peak": by_fw / ms_fw / 1e6 / peak},
             "bwd": {"ms": ms_b, "GBps": by_b / ms_b / 1e6, "frac_of_hbm_peak": by_b / ms_b / 1e6 / peak}}
 
 
