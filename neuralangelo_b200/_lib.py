@@ -94,6 +94,7 @@ def _declare(lib):
         "na_adamw_step": (ctypes.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, f32, ctypes.c_int, vp]),
         "na_adamw_step_multimem": (ctypes.c_int, [vp, vp, vp, vp, vp, i64, i64, f32, f32, f32, f32, f32, i64, f32,
                                                   ctypes.c_int, ctypes.c_int, vp]),
+        "na_linear_wgrad": (ctypes.c_int, [vp, i64, vp, i64, i64, ctypes.c_int, ctypes.c_int, vp, vp, i64, vp]),
         "na_scale_inplace": (ctypes.c_int, [vp, i64, f32, vp]),
         "na_weight_norm_fwd": (ctypes.c_int, [vp, vp, ctypes.c_int, ctypes.c_int, vp, vp, vp]),
         "na_weight_norm_bwd": (ctypes.c_int, [vp, vp, vp, vp, ctypes.c_int, ctypes.c_int, vp, vp, vp]),

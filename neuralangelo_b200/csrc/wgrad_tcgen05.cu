@@ -1,0 +1,245 @@
+// Weight gradient of a Linear layer on tcgen05:  dW[n, k] = sum_m dy[m, n] * x[m, k],  db[n] = sum_m dy[m, n].
+//
+// Replaces, for every Linear on the path, the reduction over all rows that autograd hands to a library GEMM:
+//   MLPforNeuralSDF            projects/neuralangelo/utils/mlp.py:55-69           (backward of the three linears)
+//   MLPwithSkipConnection      projects/nerf/utils/nerf_util.py:186-196           (colour MLP, both background MLPs)
+// The reference runs these products in TF32 (imaginaire/trainers/base.py:172-175 allows TF32 GEMMs); here both
+// operands are converted to fp16 (the same 10-bit mantissa) after dy has been multiplied by a power of two that lifts
+// its tiny values (1e-9 ... 1e-4) into fp16's range; products accumulate in fp32 in tensor memory.
+//
+// Shape of the problem: the reduction runs over M = 16 k ... 400 k rows, the result is at most 257 x 341 -- a library
+// GEMM has a handful of output tiles.  Here grid = (row slices, 128-column tiles of dy): a CTA walks its slice of rows
+// in steps of 64, its eight staging warps read dy[:, n-tile] and x coalesced (lanes along a row), turn eight
+// consecutive rows of one column into one 16-byte K-major chunk (the reduction index is the MMA's K) and store it in
+// the canonical no-swizzle operand layout; one elected thread issues M = 128, N = columns of x (+ one column of ones:
+// the bias gradient comes out as an extra column of dW) tcgen05.mma instructions into a [128 x <= 352] fp32
+// accumulator; at the end the slice's partial result is added to dW with 16-byte vector reductions.
+#include "tc_common.cuh"
+
+namespace {
+
+using namespace na_tc;
+
+constexpr int kStageWarps = 8;
+constexpr int kStageThreads = kStageWarps * 32;
+constexpr int kWgThreads = kStageThreads + 32;   // + MMA warp
+constexpr int kStepRows = 64;                    // rows (MMA K) per pipeline step
+constexpr int kMaxCols = 352;                    // columns of x + 1, padded to 16
+constexpr int kWgStages = 2;
+
+struct WgradArgs {
+    const float* dy;
+    int64_t ld_dy;
+    const float* x;
+    int64_t ld_x;
+    int64_t m;
+    int n_out, k_in;        // true sizes
+    int kp;                 // k_in + 1 (ones column), padded to a multiple of 16
+    const float* scale;     // device scalar (power of two) applied to dy, or null
+    float* dw;              // [n_out, ld_w] zero-initialised; column k_in receives the bias gradient
+    int64_t ld_w;           // multiple of 4
+    int64_t rows_per_cta;   // multiple of kStepRows
+};
+
+__host__ __device__ inline uint32_t wg_a_bytes() { return 128u * kStepRows * 2u; }
+__host__ __device__ inline uint32_t wg_b_bytes(int kp) { return (uint32_t)kp * kStepRows * 2u; }
+__host__ __device__ inline uint32_t wg_smem_bytes(int kp) { return kWgStages * (wg_a_bytes() + wg_b_bytes(kp)) + 256u; }
+
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+    return r;
+}
+
+__global__ void __launch_bounds__(kWgThreads, 1) linear_wgrad_kernel(const __grid_constant__ WgradArgs P) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int kp = P.kp;
+    const uint32_t a_bytes = wg_a_bytes(), b_bytes = wg_b_bytes(kp);
+    uint8_t* a_buf[kWgStages];
+    uint8_t* b_buf[kWgStages];
+    for (int s = 0; s < kWgStages; ++s) {
+        a_buf[s] = smem + s * (a_bytes + b_bytes);
+        b_buf[s] = a_buf[s] + a_bytes;
+    }
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgStages * (a_bytes + b_bytes));
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kWgStages + 1);
+    const uint32_t bar0 = smem_u32(bars);
+    auto full = [&](int s) { return bar0 + 8u * s; };
+    auto empty = [&](int s) { return bar0 + 8u * (kWgStages + s); };
+    const uint32_t done = bar0 + 8u * (2 * kWgStages);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n0 = blockIdx.y * 128;                       // first column of dy (= row of dW) of this tile
+    const int64_t m0 = (int64_t)blockIdx.x * P.rows_per_cta;
+    const int64_t m1 = min(m0 + P.rows_per_cta, P.m);
+    const int n_steps = m1 > m0 ? (int)((m1 - m0 + kStepRows - 1) / kStepRows) : 0;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kWgStages; ++s) {
+            mbar_init(full(s), kStageThreads);
+            mbar_init(empty(s), 1);
+        }
+        mbar_init(done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == kStageWarps) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == kStageWarps) {
+        // ===================== MMA issuer =====================
+        if (lane == 0 && n_steps > 0) {
+            const int n1 = kp > 256 ? 256 : kp, n2 = kp - n1;      // two column groups when x is wider than 256
+            const uint32_t idesc1 = make_idesc(128, n1), idesc2 = n2 ? make_idesc(128, n2) : 0u;
+            const uint32_t a_lbo = 128 / 8 * 128, b_lbo = (uint32_t)kp / 8 * 128;
+            for (int st = 0; st < n_steps; ++st) {
+                const int s = st % kWgStages;
+                mbar_wait(full(s), (st / kWgStages) & 1);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(a_buf[s]), b_addr = smem_u32(b_buf[s]);
+#pragma unroll
+                for (int k16 = 0; k16 < kStepRows / 16; ++k16) {
+                    const uint64_t ad = make_desc(a_addr + (uint32_t)(2 * k16) * a_lbo, a_lbo, 128);
+                    const uint64_t bd1 = make_desc(b_addr + (uint32_t)(2 * k16) * b_lbo, b_lbo, 128);
+                    const uint32_t acc = (st > 0 || k16 > 0) ? 1u : 0u;
+                    tc_mma_f16(tmem_base, ad, bd1, idesc1, acc);
+                    if (n2) {
+                        const uint64_t bd2 = make_desc(b_addr + (uint32_t)(2 * k16) * b_lbo + (256 / 8) * 128, b_lbo, 128);
+                        tc_mma_f16(tmem_base + 256, ad, bd2, idesc2, acc);
+                    }
+                }
+                tc_commit(empty(s));        // this stage's operands have been consumed
+            }
+            tc_commit(done);
+        }
+    } else {
+        // ===================== staging warps =====================
+        const float scale = P.scale ? __ldg(P.scale) : 1.f;
+        const int t = threadIdx.x;
+        const uint32_t b_kstride = (uint32_t)kp / 8 * 128;      // bytes between k-chunks of the B image
+        for (int st = 0; st < n_steps; ++st) {
+            const int s = st % kWgStages;
+            if (st >= kWgStages) mbar_wait(empty(s), ((st / kWgStages) - 1) & 1);
+            const int64_t r0 = m0 + (int64_t)st * kStepRows;
+            // ---- A: dy[r0 .. r0+63, n0 .. n0+127]: thread = (column t % 128, row half t / 128), 4 chunks of 8 rows ----
+            {
+                const int c = t & 127, half = t >> 7;
+                const bool col_ok = n0 + c < P.n_out;
+                const float* src = P.dy + (n0 + c);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int kc = half * 4 + q;                 // k-chunk (8 rows) inside the step
+                    float v[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const int64_t r = r0 + kc * 8 + e;
+                        v[e] = (col_ok && r < m1) ? __ldg(src + r * P.ld_dy) * scale : 0.f;
+                    }
+                    const uint4 pk = make_uint4(pack_h2(v[0], v[1]), pack_h2(v[2], v[3]), pack_h2(v[4], v[5]), pack_h2(v[6], v[7]));
+                    *reinterpret_cast<uint4*>(a_buf[s] + a_chunk_offset(c, kc)) = pk;
+                }
+            }
+            // ---- B: x[r0 .. r0+63, 0 .. k_in) ++ ones column ++ zero padding: thread = column, 8 chunks of 8 rows ----
+            for (int c = t; c < kp; c += kStageThreads) {
+                const bool is_x = c < P.k_in, is_one = c == P.k_in;
+                const float* src = P.x + c;
+#pragma unroll
+                for (int kc = 0; kc < kStepRows / 8; ++kc) {
+                    float v[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const int64_t r = r0 + kc * 8 + e;
+                        v[e] = r < m1 ? (is_x ? __ldg(src + r * P.ld_x) : (is_one ? 1.f : 0.f)) : 0.f;
+                    }
+                    const uint4 pk = make_uint4(pack_h2(v[0], v[1]), pack_h2(v[2], v[3]), pack_h2(v[4], v[5]), pack_h2(v[6], v[7]));
+                    const uint32_t off = (uint32_t)kc * b_kstride + (uint32_t)(c >> 3) * 128 + (uint32_t)(c & 7) * 16;
+                    *reinterpret_cast<uint4*>(b_buf[s] + off) = pk;
+                }
+            }
+            fence_proxy_async();
+            mbar_arrive(full(s));
+        }
+        // ===================== epilogue: partial result of this row slice -> dW (vector reductions) =====================
+        if (n_steps > 0) {
+            mbar_wait(done, 0);
+            tc_fence_after();
+            const float inv_scale = 1.f / scale;
+            const int quarter = warp & 3, halfw = warp >> 2;     // TMEM lanes 32 * quarter ..; column halves
+            const int row = quarter * 32 + lane;                 // row of dW inside the tile
+            const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+            const int n_chunks = kp / 16;
+            const int c_begin = halfw == 0 ? 0 : (n_chunks + 1) / 2, c_end = halfw == 0 ? (n_chunks + 1) / 2 : n_chunks;
+            const bool row_ok = n0 + row < P.n_out;
+            float* dst_row = P.dw + (int64_t)(n0 + row) * P.ld_w;
+            for (int ch = c_begin; ch < c_end; ++ch) {
+                uint32_t r[16];
+                tc_ld16(tmem_base + lane_addr + ch * 16, r);
+                tc_wait_ld();
+                if (row_ok) {
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) {
+                        const int col = ch * 16 + j;
+                        if (col + 3 <= P.k_in) {                  // all four columns real (column k_in = bias gradient)
+                            na::red_add_f4(dst_row + col,
+                                           make_float4(__uint_as_float(r[j]) * inv_scale, __uint_as_float(r[j + 1]) * inv_scale,
+                                                       __uint_as_float(r[j + 2]) * inv_scale, __uint_as_float(r[j + 3]) * inv_scale));
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e)
+                                if (col + e <= P.k_in) atomicAdd(dst_row + col + e, __uint_as_float(r[j + e]) * inv_scale);
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kStageWarps) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+}  // namespace
+
+extern "C" int na_linear_wgrad(const float* dy, int64_t ld_dy, const float* x, int64_t ld_x, int64_t m, int n_out, int k_in,
+                               const float* scale, float* dw, int64_t ld_w, void* stream) {
+    na::clear_error();
+    NA_REQUIRE(m >= 0 && n_out >= 1 && k_in >= 1, "linear_wgrad: bad sizes");
+    if (m == 0) return NA_OK;
+    NA_REQUIRE(dy && x && dw, "linear_wgrad: null pointer");
+    const int kp = (k_in + 1 + 15) / 16 * 16;
+    NA_REQUIRE(kp <= kMaxCols, "linear_wgrad: k_in %d too wide (max %d)", k_in, kMaxCols - 1);
+    NA_REQUIRE(ld_dy >= n_out && ld_x >= k_in, "linear_wgrad: leading dimensions too small");
+    NA_REQUIRE(ld_w >= k_in + 1 && ld_w % 4 == 0 && (uintptr_t)dw % 16 == 0,
+               "linear_wgrad: dw needs a 16-byte aligned base and ld_w >= k_in + 1, a multiple of 4");
+    WgradArgs P;
+    P.dy = dy, P.ld_dy = ld_dy, P.x = x, P.ld_x = ld_x, P.m = m, P.n_out = n_out, P.k_in = k_in, P.kp = kp;
+    P.scale = scale, P.dw = dw, P.ld_w = ld_w;
+    const int n_tiles = (n_out + 127) / 128;
+    // row slices: enough CTAs to fill the GPU, but no slice shorter than 4 steps (the epilogue's reductions cost about
+    // as much as two steps)
+    int64_t slices = na::kNumSMs / n_tiles;
+    if (slices < 1) slices = 1;
+    const int64_t steps = (m + kStepRows - 1) / kStepRows;
+    if (slices > (steps + 3) / 4) slices = (steps + 3) / 4;
+    if (slices < 1) slices = 1;
+    P.rows_per_cta = ((steps + slices - 1) / slices) * kStepRows;
+    slices = (m + P.rows_per_cta - 1) / P.rows_per_cta;
+    const uint32_t smem = wg_smem_bytes(kp);
+    if (int rc = na::check_cuda(cudaFuncSetAttribute(linear_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                                "linear_wgrad smem"))
+        return rc;
+    linear_wgrad_kernel<<<dim3((unsigned)slices, (unsigned)n_tiles), kWgThreads, smem, (cudaStream_t)stream>>>(P);
+    NA_CHECK_LAUNCH("linear_wgrad_kernel");
+    return NA_OK;
+}

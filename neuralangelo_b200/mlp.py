@@ -43,6 +43,30 @@ def tn_matmul(a, b):
     return a.t() @ b
 
 
+def linear_wgrad(dy, x):
+    """(dW [N,K], db [N]) of y = x W^T + b for dy [M,N], x [M,K] on the tcgen05 weight-gradient kernel
+    (na_linear_wgrad): one launch, fp16 operands (TF32-class mantissa) with dy pre-scaled by a power of two taken from
+    its largest magnitude (device-side, no host synchronisation), fp32 accumulation."""
+    from . import _lib
+    m, n = dy.shape
+    k = x.shape[1]
+    dy = dy if dy.stride(1) == 1 else dy.contiguous()
+    x = x if x.stride(1) == 1 else x.contiguous()
+    ld_w = (k + 1 + 3) // 4 * 4
+    out = torch.zeros(n, ld_w, dtype=torch.float32, device=dy.device)
+    # 2^floor(log2(4096 / max|dy|)): the largest entry lands in [2048, 4096), far from fp16's 65504
+    amax = dy.detach().abs().amax().clamp_min(1e-30)
+    scale = torch.exp2(torch.floor(torch.log2(4096.0 / amax))).reshape(1).float()
+    _lib.check(_lib.lib().na_linear_wgrad(_lib.ptr(dy), dy.stride(0), _lib.ptr(x), x.stride(0), m, n, k, _lib.ptr(scale),
+                                          _lib.ptr(out), ld_w, _lib.current_stream()), "na_linear_wgrad")
+    return out[:, :k], out[:, k]
+
+
+def wgrad_supported(dy, x):
+    return dy.is_cuda and dy.dtype == torch.float32 and x.dtype == torch.float32 and x.shape[1] <= 351 and \
+        dy.dim() == 2 and x.dim() == 2
+
+
 def colsum(a):
     """a.sum(dim=0) of a tall contiguous [M,p] matrix (a bias gradient).  ATen's reduction over the slow dimension
     runs at a quarter of the HBM bandwidth for M >= 65536 (measured on B200: 168 us for 262144 x 256 fp32); summing 64

@@ -247,3 +247,26 @@ def test_fused_weight_norm_forward_and_backward(na_lib, cuda_device, rows, cols)
     torch.testing.assert_close(vk.grad.cpu().double(), vd.grad, rtol=2e-5, atol=2e-6)
     torch.testing.assert_close(gk.grad.cpu().double(), gd.grad, rtol=2e-5, atol=2e-6)
     assert gk.grad.shape == (rows, 1)
+
+
+@pytest.mark.parametrize("m,n,k", [(8192, 256, 131), (70001, 256, 278), (4096, 257, 340), (1000, 3, 256), (333, 1, 256),
+                                   (65536, 128, 16), (50, 64, 351)])
+def test_linear_wgrad_kernel_vs_float64(na_lib, cuda_device, m, n, k):
+    """na_linear_wgrad (tcgen05, fp16 operands, fp32 accumulation) against a float64 product.  Tolerance: the operands
+    carry 11 significant bits (as TF32), errors are independent over the m terms of a sum: 2e-3 of the largest entry."""
+    from neuralangelo_b200.mlp import linear_wgrad
+    g = torch.Generator(device=cuda_device).manual_seed(m + n + k)
+    # gradients as the renderer produces them: tiny, with a heavy tail
+    dy = torch.randn(m, n, device=cuda_device, generator=g) * 1e-6 * torch.exp(2 * torch.randn(m, 1, device=cuda_device, generator=g))
+    x = torch.relu(torch.randn(m, k, device=cuda_device, generator=g)) * 3.0
+    dw, db = linear_wgrad(dy, x)
+    ref_w = dy.double().t() @ x.double()
+    ref_b = dy.double().sum(0)
+    assert dw.shape == (n, k) and db.shape == (n,)
+    assert (dw.double() - ref_w).abs().max().item() <= 2e-3 * ref_w.abs().max().item()
+    assert (db.double() - ref_b).abs().max().item() <= 2e-3 * ref_b.abs().max().item() + 1e-12
+    # strided inputs (a column slice of a wider buffer), as the skip-connection layers pass them
+    wide = torch.zeros(m, k + 5, device=cuda_device)
+    wide[:, 2:2 + k] = x
+    dw2, db2 = linear_wgrad(dy, wide[:, 2:2 + k])
+    torch.testing.assert_close(dw2, dw, rtol=0, atol=1e-6 * dw.abs().max().item())
