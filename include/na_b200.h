@@ -232,14 +232,14 @@ int na_mc_run_static(const float* volume, int nx, int ny, int nz, double iso, do
 /* Weight and bias gradient of a Linear layer, y = x W^T + b, on tcgen05 (csrc/wgrad_tcgen05.cu):
  *   dw[n*ld_w + k] += sum_m dy[m*ld_dy + n] * x[m*ld_x + k]   (k < k_in),      dw[n*ld_w + k_in] += sum_m dy[m*ld_dy + n]
  * i.e. the bias gradient arrives as column k_in of the same buffer.  `dw` must be ZERO-FILLED by the caller (row slices
- * add their partial sums with vector reductions), 16-byte aligned, ld_w >= k_in + 1 and a multiple of 4.  `scale`: device
- * scalar, a power of two by which dy is multiplied before its conversion to fp16 (the result is divided by it again);
- * NULL = 1.  Operands in fp16 (10-bit mantissa, as the TF32 GEMMs the reference runs), accumulation in fp32.
- * k_in <= 351, any n_out, any m.
+ * add their partial sums with vector reductions), 16-byte aligned, ld_w >= k_in + 1 and a multiple of 4.  `amax`: device
+ * scalar holding max|dy|; dy is multiplied by 2^floor(log2(4096 / amax)) before its conversion to fp16 and the result
+ * divided by it again (NULL = no scaling).  Operands of dW in fp16 (10-bit mantissa, as the TF32 GEMMs the reference
+ * runs), accumulation in fp32; the bias gradient is an fp32 sum of the unconverted dy.  k_in <= 352, any n_out, any m.
  * Replaces: autograd's weight-gradient GEMM + bias-gradient reduction of every nn.Linear on the path
  * (projects/neuralangelo/utils/mlp.py:55-69, projects/nerf/utils/nerf_util.py:186-196). */
 int na_linear_wgrad(const float* dy, int64_t ld_dy, const float* x, int64_t ld_x, int64_t m, int n_out, int k_in,
-                    const float* scale, float* dw, int64_t ld_w, void* stream);
+                    const float* amax, float* dw, int64_t ld_w, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Optimizer step.

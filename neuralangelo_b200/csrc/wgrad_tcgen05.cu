@@ -11,9 +11,10 @@
 // GEMM has a handful of output tiles.  Here grid = (row slices, 128-column tiles of dy): a CTA walks its slice of rows
 // in steps of 64, its eight staging warps read dy[:, n-tile] and x coalesced (lanes along a row), turn eight
 // consecutive rows of one column into one 16-byte K-major chunk (the reduction index is the MMA's K) and store it in
-// the canonical no-swizzle operand layout; one elected thread issues M = 128, N = columns of x (+ one column of ones:
-// the bias gradient comes out as an extra column of dW) tcgen05.mma instructions into a [128 x <= 352] fp32
-// accumulator; at the end the slice's partial result is added to dW with 16-byte vector reductions.
+// the canonical no-swizzle operand layout; one elected thread issues M = 128, N = columns of x tcgen05.mma
+// instructions into a [128 x <= 352] fp32 accumulator; at the end the slice's partial result is added to dW with 16-byte
+// vector reductions.  The bias gradient is the fp32 column sum of dy, accumulated by the staging threads on the way
+// (exact products: sums that nearly cancel, like the SDF head's bias, keep their accuracy).
 #include "tc_common.cuh"
 
 namespace {
@@ -24,7 +25,7 @@ constexpr int kStageWarps = 8;
 constexpr int kStageThreads = kStageWarps * 32;
 constexpr int kWgThreads = kStageThreads + 32;   // + MMA warp
 constexpr int kStepRows = 64;                    // rows (MMA K) per pipeline step
-constexpr int kMaxCols = 352;                    // columns of x + 1, padded to 16
+constexpr int kMaxCols = 352;                    // columns of x, padded to 16
 constexpr int kWgStages = 2;
 
 struct WgradArgs {
@@ -34,8 +35,8 @@ struct WgradArgs {
     int64_t ld_x;
     int64_t m;
     int n_out, k_in;        // true sizes
-    int kp;                 // k_in + 1 (ones column), padded to a multiple of 16
-    const float* scale;     // device scalar (power of two) applied to dy, or null
+    int kp;                 // k_in padded to a multiple of 16
+    const float* scale;     // device scalar max|dy| (the kernel derives a power-of-two scale from it), or null
     float* dw;              // [n_out, ld_w] zero-initialised; column k_in receives the bias gradient
     int64_t ld_w;           // multiple of 4
     int64_t rows_per_cta;   // multiple of kStepRows
@@ -121,51 +122,65 @@ __global__ void __launch_bounds__(kWgThreads, 1) linear_wgrad_kernel(const __gri
         }
     } else {
         // ===================== staging warps =====================
-        const float scale = P.scale ? __ldg(P.scale) : 1.f;
+        // dy is multiplied by 2^floor(log2(4096 / max|dy|)) (max|dy| read from device memory) before its conversion
+        float scale = 1.f;
+        if (P.scale) {
+            const float amax = __ldg(P.scale);
+            if (amax > 0.f && amax < 3.0e38f) scale = exp2f(floorf(log2f(4096.f / amax)));
+        }
         const int t = threadIdx.x;
         const uint32_t b_kstride = (uint32_t)kp / 8 * 128;      // bytes between k-chunks of the B image
+        const int ca = t & 127, half = t >> 7;                   // A: column of the tile and which 32 of the 64 rows
+        const bool col_ok = n0 + ca < P.n_out;
+        float bias_acc = 0.f;                                    // fp32 column sum of dy: the bias gradient, exact products
         for (int st = 0; st < n_steps; ++st) {
             const int s = st % kWgStages;
             if (st >= kWgStages) mbar_wait(empty(s), ((st / kWgStages) - 1) & 1);
             const int64_t r0 = m0 + (int64_t)st * kStepRows;
-            // ---- A: dy[r0 .. r0+63, n0 .. n0+127]: thread = (column t % 128, row half t / 128), 4 chunks of 8 rows ----
+            // ---- A: dy[r0 .. r0+63, n0 .. n0+127]: thread = (column, row half); all 32 loads in flight, then 4 chunks ----
             {
-                const int c = t & 127, half = t >> 7;
-                const bool col_ok = n0 + c < P.n_out;
-                const float* src = P.dy + (n0 + c);
+                const float* src = P.dy + (n0 + ca);
+                float v[32];
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                    const int64_t r = r0 + half * 32 + e;
+                    v[e] = (col_ok && r < m1) ? __ldg(src + r * P.ld_dy) : 0.f;
+                }
+#pragma unroll
+                for (int e = 0; e < 32; ++e) bias_acc += v[e];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const int kc = half * 4 + q;                 // k-chunk (8 rows) inside the step
-                    float v[8];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const int64_t r = r0 + kc * 8 + e;
-                        v[e] = (col_ok && r < m1) ? __ldg(src + r * P.ld_dy) * scale : 0.f;
-                    }
-                    const uint4 pk = make_uint4(pack_h2(v[0], v[1]), pack_h2(v[2], v[3]), pack_h2(v[4], v[5]), pack_h2(v[6], v[7]));
-                    *reinterpret_cast<uint4*>(a_buf[s] + a_chunk_offset(c, kc)) = pk;
+                    const float* w = v + q * 8;
+                    const uint4 pk = make_uint4(pack_h2(w[0] * scale, w[1] * scale), pack_h2(w[2] * scale, w[3] * scale),
+                                                pack_h2(w[4] * scale, w[5] * scale), pack_h2(w[6] * scale, w[7] * scale));
+                    *reinterpret_cast<uint4*>(a_buf[s] + a_chunk_offset(ca, half * 4 + q)) = pk;
                 }
             }
-            // ---- B: x[r0 .. r0+63, 0 .. k_in) ++ ones column ++ zero padding: thread = column, 8 chunks of 8 rows ----
+            // ---- B: x[r0 .. r0+63, 0 .. k_in) ++ zero padding: thread = column, two batches of 32 rows ----
             for (int c = t; c < kp; c += kStageThreads) {
-                const bool is_x = c < P.k_in, is_one = c == P.k_in;
+                const bool is_x = c < P.k_in;
                 const float* src = P.x + c;
 #pragma unroll
-                for (int kc = 0; kc < kStepRows / 8; ++kc) {
-                    float v[8];
+                for (int hb = 0; hb < 2; ++hb) {
+                    float v[32];
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const int64_t r = r0 + kc * 8 + e;
-                        v[e] = r < m1 ? (is_x ? __ldg(src + r * P.ld_x) : (is_one ? 1.f : 0.f)) : 0.f;
+                    for (int e = 0; e < 32; ++e) {
+                        const int64_t r = r0 + hb * 32 + e;
+                        v[e] = (is_x && r < m1) ? __ldg(src + r * P.ld_x) : 0.f;
                     }
-                    const uint4 pk = make_uint4(pack_h2(v[0], v[1]), pack_h2(v[2], v[3]), pack_h2(v[4], v[5]), pack_h2(v[6], v[7]));
-                    const uint32_t off = (uint32_t)kc * b_kstride + (uint32_t)(c >> 3) * 128 + (uint32_t)(c & 7) * 16;
-                    *reinterpret_cast<uint4*>(b_buf[s] + off) = pk;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float* w = v + q * 8;
+                        const uint4 pk = make_uint4(pack_h2(w[0], w[1]), pack_h2(w[2], w[3]), pack_h2(w[4], w[5]), pack_h2(w[6], w[7]));
+                        const uint32_t off = (uint32_t)(hb * 4 + q) * b_kstride + (uint32_t)(c >> 3) * 128 + (uint32_t)(c & 7) * 16;
+                        *reinterpret_cast<uint4*>(b_buf[s] + off) = pk;
+                    }
                 }
             }
             fence_proxy_async();
             mbar_arrive(full(s));
         }
+        if (col_ok && n_steps > 0) atomicAdd(P.dw + (int64_t)(n0 + ca) * P.ld_w + P.k_in, bias_acc);
         // ===================== epilogue: partial result of this row slice -> dW (vector reductions) =====================
         if (n_steps > 0) {
             mbar_wait(done, 0);
@@ -186,14 +201,14 @@ __global__ void __launch_bounds__(kWgThreads, 1) linear_wgrad_kernel(const __gri
 #pragma unroll
                     for (int j = 0; j < 16; j += 4) {
                         const int col = ch * 16 + j;
-                        if (col + 3 <= P.k_in) {                  // all four columns real (column k_in = bias gradient)
+                        if (col + 3 < P.k_in) {                   // all four columns real
                             na::red_add_f4(dst_row + col,
                                            make_float4(__uint_as_float(r[j]) * inv_scale, __uint_as_float(r[j + 1]) * inv_scale,
                                                        __uint_as_float(r[j + 2]) * inv_scale, __uint_as_float(r[j + 3]) * inv_scale));
                         } else {
 #pragma unroll
                             for (int e = 0; e < 4; ++e)
-                                if (col + e <= P.k_in) atomicAdd(dst_row + col + e, __uint_as_float(r[j + e]) * inv_scale);
+                                if (col + e < P.k_in) atomicAdd(dst_row + col + e, __uint_as_float(r[j + e]) * inv_scale);
                         }
                     }
                 }
@@ -209,6 +224,40 @@ __global__ void __launch_bounds__(kWgThreads, 1) linear_wgrad_kernel(const __gri
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Heads (n_out <= 4: the SDF value, the colour triple): dW is a handful of matrix-vector products whose terms nearly
+// cancel (d_sdf changes sign along every ray), so they are summed in plain fp32 on the CUDA cores -- a pure streaming
+// pass over x, one thread per column of x, dy broadcast.
+// ---------------------------------------------------------------------------------------------
+template <int NOUT>
+__global__ void __launch_bounds__(256)
+linear_wgrad_head_kernel(const float* __restrict__ dy, int64_t ld_dy, const float* __restrict__ x, int64_t ld_x, int64_t m,
+                         int k_in, float* __restrict__ dw, int64_t ld_w, int64_t rows_per_cta) {
+    const int64_t m0 = (int64_t)blockIdx.x * rows_per_cta, m1 = min(m0 + rows_per_cta, m);
+    const int c0 = threadIdx.x, c1 = threadIdx.x + 256;
+    const bool ok0 = c0 < k_in, ok1 = c1 < k_in;
+    float acc0[NOUT], acc1[NOUT], bsum[NOUT];
+#pragma unroll
+    for (int n = 0; n < NOUT; ++n) acc0[n] = acc1[n] = bsum[n] = 0.f;
+#pragma unroll 4
+    for (int64_t r = m0; r < m1; ++r) {
+        const float x0 = ok0 ? __ldg(x + r * ld_x + c0) : 0.f, x1 = ok1 ? __ldg(x + r * ld_x + c1) : 0.f;
+#pragma unroll
+        for (int n = 0; n < NOUT; ++n) {
+            const float d = __ldg(dy + r * ld_dy + n);
+            acc0[n] = fmaf(d, x0, acc0[n]);
+            acc1[n] = fmaf(d, x1, acc1[n]);
+            bsum[n] += d;
+        }
+    }
+#pragma unroll
+    for (int n = 0; n < NOUT; ++n) {
+        if (ok0) atomicAdd(dw + n * ld_w + c0, acc0[n]);
+        if (ok1) atomicAdd(dw + n * ld_w + c1, acc1[n]);
+        if (threadIdx.x == 0) atomicAdd(dw + n * ld_w + k_in, bsum[n]);
+    }
+}
+
 }  // namespace
 
 extern "C" int na_linear_wgrad(const float* dy, int64_t ld_dy, const float* x, int64_t ld_x, int64_t m, int n_out, int k_in,
@@ -217,11 +266,26 @@ extern "C" int na_linear_wgrad(const float* dy, int64_t ld_dy, const float* x, i
     NA_REQUIRE(m >= 0 && n_out >= 1 && k_in >= 1, "linear_wgrad: bad sizes");
     if (m == 0) return NA_OK;
     NA_REQUIRE(dy && x && dw, "linear_wgrad: null pointer");
-    const int kp = (k_in + 1 + 15) / 16 * 16;
-    NA_REQUIRE(kp <= kMaxCols, "linear_wgrad: k_in %d too wide (max %d)", k_in, kMaxCols - 1);
+    const int kp = (k_in + 15) / 16 * 16;
+    NA_REQUIRE(kp <= kMaxCols, "linear_wgrad: k_in %d too wide (max %d)", k_in, kMaxCols);
     NA_REQUIRE(ld_dy >= n_out && ld_x >= k_in, "linear_wgrad: leading dimensions too small");
     NA_REQUIRE(ld_w >= k_in + 1 && ld_w % 4 == 0 && (uintptr_t)dw % 16 == 0,
                "linear_wgrad: dw needs a 16-byte aligned base and ld_w >= k_in + 1, a multiple of 4");
+    if (n_out <= 4 && k_in <= 512) {
+        int64_t slices = (int64_t)na::kNumSMs * 4;
+        int64_t rows = (m + slices - 1) / slices;
+        if (rows < 64) rows = 64;
+        slices = (m + rows - 1) / rows;
+        cudaStream_t s = (cudaStream_t)stream;
+        switch (n_out) {
+            case 1: linear_wgrad_head_kernel<1><<<(unsigned)slices, 256, 0, s>>>(dy, ld_dy, x, ld_x, m, k_in, dw, ld_w, rows); break;
+            case 2: linear_wgrad_head_kernel<2><<<(unsigned)slices, 256, 0, s>>>(dy, ld_dy, x, ld_x, m, k_in, dw, ld_w, rows); break;
+            case 3: linear_wgrad_head_kernel<3><<<(unsigned)slices, 256, 0, s>>>(dy, ld_dy, x, ld_x, m, k_in, dw, ld_w, rows); break;
+            default: linear_wgrad_head_kernel<4><<<(unsigned)slices, 256, 0, s>>>(dy, ld_dy, x, ld_x, m, k_in, dw, ld_w, rows); break;
+        }
+        NA_CHECK_LAUNCH("linear_wgrad_head_kernel");
+        return NA_OK;
+    }
     WgradArgs P;
     P.dy = dy, P.ld_dy = ld_dy, P.x = x, P.ld_x = ld_x, P.m = m, P.n_out = n_out, P.k_in = k_in, P.kp = kp;
     P.scale = scale, P.dw = dw, P.ld_w = ld_w;

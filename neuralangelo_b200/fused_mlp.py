@@ -9,7 +9,7 @@ import torch
 
 from . import _lib
 from ._lib import ptr
-from .mlp import colsum, tn_matmul
+from .mlp import colsum, linear_wgrad, tn_matmul, wgrad_supported
 
 _L = _lib.lib
 LO_SCALE = 2048.0
@@ -195,12 +195,17 @@ class FusedSdfMlpFunction(torch.autograd.Function):
             _lib.check(rc, "na_sdf_mlp_bwd")
             # weight gradients: reductions over the rows, in the ambient matmul precision (TrainStep enables TF32 by
             # default, as the reference's trainer does: imaginaire/trainers/base.py:172-175)
-            dw0 = tn_matmul(dz0, rows)
-            db0 = colsum(dz0)
-            dw1 = tn_matmul(dz1, hidden) if two else None
-            db1 = colsum(dz1) if two else None
-            dwh = (d_sdf[None, :] @ hidden)
-            dbh = d_sdf.sum().reshape(1)
+            if wgrad_supported(dz0, rows):      # tcgen05 weight-gradient kernel (csrc/wgrad_tcgen05.cu)
+                dw0, db0 = linear_wgrad(dz0, rows)
+                dw1, db1 = linear_wgrad(dz1, hidden) if two else (None, None)
+                dwh, dbh = linear_wgrad(d_sdf[:, None], hidden)
+            else:
+                dw0 = tn_matmul(dz0, rows)
+                db0 = colsum(dz0)
+                dw1 = tn_matmul(dz1, hidden) if two else None
+                db1 = colsum(dz1) if two else None
+                dwh = (d_sdf[None, :] @ hidden)
+                dbh = d_sdf.sum().reshape(1)
         return dx, dw0, db0, dw1, db1, dwh, dbh, None, None, None
 
 
