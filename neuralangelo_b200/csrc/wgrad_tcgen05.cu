@@ -52,7 +52,9 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
     return r;
 }
 
-__global__ void __launch_bounds__(kWgThreads, 1) linear_wgrad_kernel(const __grid_constant__ WgradArgs P) {
+// Two CTAs per SM where shared and tensor memory allow it (x at most 256 columns wide: 96 KB and 256 TMEM columns each):
+// the kernel waits on its global loads (ncu: long_scoreboard, 9 resident warps), a second CTA doubles what is in flight.
+__global__ void __launch_bounds__(kWgThreads, 2) linear_wgrad_kernel(const __grid_constant__ WgradArgs P) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const int kp = P.kp;
     const uint32_t a_bytes = wg_a_bytes(), b_bytes = wg_b_bytes(kp);
@@ -85,7 +87,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) linear_wgrad_kernel(const __gri
     }
     if (warp == kStageWarps) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"(512u)
+                     "r"(kp <= 256 ? 256u : 512u)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -220,7 +222,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) linear_wgrad_kernel(const __gri
     __syncthreads();
     if (warp == kStageWarps) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kp <= 256 ? 256u : 512u)
+                     : "memory");
     }
 }
 
@@ -292,7 +295,7 @@ extern "C" int na_linear_wgrad(const float* dy, int64_t ld_dy, const float* x, i
     const int n_tiles = (n_out + 127) / 128;
     // row slices: enough CTAs to fill the GPU, but no slice shorter than 4 steps (the epilogue's reductions cost about
     // as much as two steps)
-    int64_t slices = na::kNumSMs / n_tiles;
+    int64_t slices = (int64_t)na::kNumSMs * (kp <= 256 ? 2 : 1) / n_tiles;
     if (slices < 1) slices = 1;
     const int64_t steps = (m + kStepRows - 1) / kStepRows;
     if (slices > (steps + 3) / 4) slices = (steps + 3) / 4;
