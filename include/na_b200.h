@@ -326,14 +326,17 @@ int na_sdf_mlp_bwd(int64_t m, int n, int k0, int k0_pad, int two_layer, const fl
                    int64_t ld_dx, void* stream);
 
 /* ------------------------------------------------------------------------------------------
- * Generic fused MLP forward on tcgen05: a program of stages run per 128-row tile with all intermediate
- * activations on chip.  Stage = [epilogue of the previous product: + bias, activation (0 none, 1 relu,
- * 2 softplus(act_param), 3 sigmoid) -> next A operand (epi_to_a) and/or global `out` and/or `save`]
+ * Generic fused MLP chain on tcgen05: a program of stages run per 128-row tile with all intermediate
+ * activations on chip; the same kernel runs the forward of a network and the input-gradient chain of its backward.
+ * Stage = [epilogue of the previous product: + bias, activation (0 none, 1 relu, 2 softplus(act_param), 3 sigmoid,
+ * 4 relu-mask: no bias, the accumulator -- an upstream gradient -- is passed where the layer's saved activation,
+ * READ from `save`, is positive) -> next A operand (epi_to_a) and/or global `out` and/or (acts 0-3) `save`]
  * [load in_cols (<= 256) columns of a global input into the A operand] [product D (+)= A W^T, n_out <= 256,
  * k_chunks*8 <= 256 columns of A; weights packed like na_sdf_mlp_fwd's].  Wide inputs, skip connections,
  * 257-wide layers and chained networks are sequences of such stages (see neuralangelo_b200/fused_chain.py).
  * Replaces: MLPwithSkipConnection.forward, projects/nerf/utils/nerf_util.py:186-196, as used by
- *   NeuralRGB.forward (projects/neuralangelo/utils/modules.py:209-220) and BackgroundNeRF.forward (:270-285).
+ *   NeuralRGB.forward (projects/neuralangelo/utils/modules.py:209-220) and BackgroundNeRF.forward (:270-285),
+ *   and autograd's dX = dY W chain through the same layers.
  * ---------------------------------------------------------------------------------------- */
 typedef struct na_mlp_stage {
     int32_t has_epi, act, n_valid, epi_to_a;

@@ -30,7 +30,9 @@ constexpr int kBStageBytes = 2 * kMaxN * kBlockK * 2;
 constexpr int kSmemBytes = 2 * kABytes + kStages * kBStageBytes + 1024;
 constexpr int kMaxProgram = 20;
 
-enum Act { kNone = 0, kRelu = 1, kSoftplus = 2, kSigmoid = 3 };
+// kReluMask: backward link of a relu layer -- the accumulator (an upstream gradient) is multiplied by the step function
+// of the layer's SAVED activation, which is READ from the stage's `save` pointer (no bias is added)
+enum Act { kNone = 0, kRelu = 1, kSoftplus = 2, kSigmoid = 3, kReluMask = 4 };
 
 struct Stage {
     // epilogue of the previous stage's product
@@ -203,12 +205,22 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_fwd_kernel(const __grid
                         tc_ld32(d_cross + lane_addr + c0, rc);
                         tc_wait_ld();
                         float act[32];
+                        if (S.act == kReluMask) {
+                            const float* mk = S.save + grow * S.save_ld + c0;
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const bool real = c0 + j < S.n_valid;
-                            const float pre = fmaf(__uint_as_float(rc[j]), kLoInv, __uint_as_float(rm[j])) +
-                                              (real ? __ldg(S.bias + c0 + j) : 0.f);
-                            act[j] = real ? activate(pre, S.act, S.act_param) : 0.f;
+                            for (int j = 0; j < 32; ++j) {
+                                const bool real = valid && c0 + j < S.n_valid;
+                                const float g = fmaf(__uint_as_float(rc[j]), kLoInv, __uint_as_float(rm[j]));
+                                act[j] = (real && __ldg(mk + j) > 0.f) ? g : 0.f;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const bool real = c0 + j < S.n_valid;
+                                const float pre = fmaf(__uint_as_float(rc[j]), kLoInv, __uint_as_float(rm[j])) +
+                                                  (real ? __ldg(S.bias + c0 + j) : 0.f);
+                                act[j] = real ? activate(pre, S.act, S.act_param) : 0.f;
+                            }
                         }
                         if (S.epi_to_a) {
 #pragma unroll
@@ -230,7 +242,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_fwd_kernel(const __grid
                                 for (int j = 0; j < 32; ++j)
                                     if (c0 + j < S.n_valid) dst[j] = act[j];
                             }
-                            if (S.save) {
+                            if (S.save && S.act != kReluMask) {
                                 float* dst = S.save + grow * S.save_ld + c0;
 #pragma unroll
                                 for (int j = 0; j < 32; ++j)
@@ -320,7 +332,8 @@ extern "C" int na_mlp_chain_fwd(const na_mlp_stage* stages, int n_stages, int64_
         if (S.has_epi) {
             NA_REQUIRE(have_product, "mlp_chain_fwd: stage %d has an epilogue but no product precedes it", i);
             NA_REQUIRE(S.bias && S.n_valid >= 1 && S.n_valid <= kMaxN, "mlp_chain_fwd: stage %d epilogue arguments", i);
-            NA_REQUIRE(S.act >= kNone && S.act <= kSigmoid, "mlp_chain_fwd: stage %d unknown activation %d", i, S.act);
+            NA_REQUIRE(S.act >= kNone && S.act <= kReluMask, "mlp_chain_fwd: stage %d unknown activation %d", i, S.act);
+            NA_REQUIRE(S.act != kReluMask || S.save, "mlp_chain_fwd: stage %d relu-mask epilogue needs the saved activation", i);
             NA_REQUIRE(S.act != kSoftplus || S.act_param > 0.f, "mlp_chain_fwd: stage %d softplus beta", i);
         }
         if (S.in) NA_REQUIRE(S.in_cols >= 1 && S.in_cols <= kMaxK && S.in_col >= 0, "mlp_chain_fwd: stage %d input columns", i);

@@ -319,11 +319,14 @@ class NeuralSDF(torch.nn.Module):
         return gradient, hessian
 
 
-# The colour / background networks run on the tcgen05 chain kernel whenever no autograd graph is needed
-# (validation renders, texture extraction).  With a graph the default is the reference's own arithmetic -- library
-# GEMMs, TF32 when the trainer allows it (imaginaire/trainers/base.py:172-175): measured on B200 the fused forward
-# with saved activations plus a library backward is ~8 % slower per training step than cuBLAS TF32 end to end
-# (profiles/r01_measurements.md), so it is opt-in until the backward is fused as well.
+# The colour / background networks run on the tcgen05 chain kernel (csrc/mlp_chain.cu) whenever no autograd graph is
+# needed (validation renders, texture extraction): one launch per network.  With a graph (training) the same kernel can
+# run the forward (saving the layer activations) and, as a second stage program with relu-mask epilogues, the
+# input-gradient chain (fused_chain.FusedMlpFunction) -- parity-tested, but measured SLOWER than the library path on
+# B200 (default config, 512 rays: forward+backward 6.85 ms against 5.14 ms with TF32 library GEMMs, plus 1.8 ms per
+# step of operand re-packing; profiles/r02_training.md): the chain kernel runs its stages one after the other on a
+# single accumulator and pays three fp16 MMAs per product.  So it stays opt-in; the weight and bias gradients of these
+# networks run on the tcgen05 weight-gradient kernel either way (mlp.linear_wgrad).
 FUSED_CHAIN_IN_TRAINING = False
 
 

@@ -7,7 +7,7 @@ without the generic trainer framework (checkpointing, logging, data loading: out
 import torch
 import torch.nn.functional as torch_F
 
-from . import parallel
+from . import fused_chain, parallel
 from .model import curvature_loss, eikonal_loss
 from .optim import FusedAdamW
 
@@ -175,6 +175,11 @@ class TrainStep:
             grad_scale = parallel.allreduce_gradients(*self.optim.grad_views())
             self.optim.step(grad_scale=grad_scale, lr=lr)
         self.model.neural_sdf.refresh_packed_weights()   # outside any captured graph (see NeuralSDF)
+        from . import modules
+        if modules.FUSED_CHAIN_IN_TRAINING:
+            fused_chain.refresh_packs()      # colour / background operands re-packed in place, outside the captured graph
+        else:
+            fused_chain.invalidate_packs()   # only graph-free evaluations use them: re-pack lazily at the next use
         if ev:
             ev[2].record()
         self.current_iteration += 1

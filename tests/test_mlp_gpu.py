@@ -202,7 +202,9 @@ def test_fused_chain_colour_mlp_forward_and_backward(na_lib, cuda_device):
     assert (xk.grad.cpu().double() - xd.grad).abs().max().item() <= 1e-5 * xd.grad.abs().max().item() + 1e-9
     for k, p in mlp.named_parameters():
         rel = (p.grad.cpu().double() - ref_g[k]).norm().item() / max(ref_g[k].norm().item(), 1e-30)
-        assert rel <= 1e-5, (k, rel)       # fp32 library GEMMs in this test (conftest disables TF32)
+        # input-gradient chain: split-fp16 products (fp32-grade, checked on dx above); weight gradients: fp16 operands
+        # with fp32 accumulation (11 significant bits, the class of the reference's TF32 products), biases fp32 sums
+        assert rel <= (1e-5 if k.endswith("bias") else 2e-3), (k, rel)
 
 
 def test_fused_chain_background_nerf(na_lib, cuda_device):
