@@ -354,6 +354,39 @@ typedef struct na_mlp_stage {
 } na_mlp_stage;
 int na_mlp_chain_fwd(const na_mlp_stage* stages, int n_stages, int64_t m, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Element-wise glue of the per-ray pipeline, one launch each (csrc/glue.cu).  All tensors fp32 contiguous unless a
+ * leading dimension is given; `rows` = rays x samples, `samples_per_ray` maps a row to its ray.
+ * ---------------------------------------------------------------------------------------- */
+
+/* out[row] = [xyz(3) | SH_levels(ray_unit of the row's ray) | grad / max(|grad|, 1e-12) (3) | feat(n_feat) | app(n_app)]:
+ * the colour network's input.  Replaces: NeuralRGB.forward's encode_view + cat (projects/neuralangelo/utils/modules.py:
+ * 209-229, spherical_harmonics.py:47-84) and the F.normalize of projects/neuralangelo/model.py:181. */
+int na_rgb_input_fwd(const float* points, const float* ray_unit, const float* grad, const float* feat, int64_t ld_feat,
+                     const float* app, int64_t ld_app, int64_t rows, int samples_per_ray, int sh_levels, int n_feat,
+                     int n_app, float* out, int64_t ld_out, void* stream);
+/* d_grad[row] from the three normal columns (first at `normal_col`) of d_out: the adjoint of the normalisation.  The
+ * gradient of feat is the corresponding column block of d_out itself. */
+int na_rgb_input_bwd(const float* grad, const float* d_out, int64_t ld_out, int normal_col, int64_t rows, float* d_grad,
+                     void* stream);
+
+/* Finite-difference gradient and curvature from tap SDF values taps[T][rows] and the centre sdf[rows]:
+ * T = 6 (+x -x +y -y +z -z): grad_a = (s_2a - s_2a+1) / den_grad, hess_a = (s_2a + s_2a+1 - 2 sdf) / den_hess;
+ * T = 4 (tetrahedral stencil): grad = sum_i k_i s_i / den_grad, hess = ((sum_i s_i) / 2 - 2 sdf) / den_hess / 3 (x3).
+ * hess may be NULL.  Replaces: the tensor arithmetic of NeuralSDF.compute_gradients, modules.py:144-175. */
+int na_tap_combine_fwd(const float* taps, const float* sdf, int64_t rows, int n_taps, float den_grad, float den_hess,
+                       float* grad, float* hess, void* stream);
+int na_tap_combine_bwd(const float* d_grad, const float* d_hess, int64_t rows, int n_taps, float den_grad,
+                       float den_hess, float* d_taps, float* d_sdf, void* stream);
+
+/* out2[0] += mean over rows of nan_to_num((|grad| - 1)^2), out2[1] += mean of nan_to_num(|hess_x + hess_y + hess_z|)
+ * (hess may be NULL), rows of rays with outside[ray] != 0 contributing zero; out2 zero-filled by the caller.
+ * Replaces: eikonal_loss / curvature_loss, projects/neuralangelo/utils/misc.py:74-89. */
+int na_sdf_losses_fwd(const float* grad, const float* hess, const uint8_t* outside, int64_t rows, int samples_per_ray,
+                      float* out2, void* stream);
+int na_sdf_losses_bwd(const float* grad, const float* hess, const uint8_t* outside, int64_t rows, int samples_per_ray,
+                      const float* d_out2, float* d_grad, float* d_hess, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

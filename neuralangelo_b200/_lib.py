@@ -105,6 +105,13 @@ def _declare(lib):
         "na_sdf_mlp_bwd": (ctypes.c_int, [i64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, vp, vp, i64, vp,
                                           vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, i64, vp]),
         "na_mlp_chain_fwd": (ctypes.c_int, [ctypes.POINTER(MlpStage), ctypes.c_int, i64, vp]),
+        "na_rgb_input_fwd": (ctypes.c_int, [vp, vp, vp, vp, i64, vp, i64, i64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                            ctypes.c_int, vp, i64, vp]),
+        "na_rgb_input_bwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, i64, vp, vp]),
+        "na_tap_combine_fwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, f32, f32, vp, vp, vp]),
+        "na_tap_combine_bwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, f32, f32, vp, vp, vp]),
+        "na_sdf_losses_fwd": (ctypes.c_int, [vp, vp, vp, i64, ctypes.c_int, vp, vp]),
+        "na_sdf_losses_bwd": (ctypes.c_int, [vp, vp, vp, i64, ctypes.c_int, vp, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -153,10 +153,9 @@ class Model(torch.nn.Module):
         points = camera.get_3D_points_from_dist(center, ray_unit, dists)  # [B,R,N,3]
         sdfs, feats = self.neural_sdf.forward(points)
         sdfs = torch.where(outside[..., None].expand_as(sdfs), torch.full_like(sdfs, self.outside_val), sdfs)
-        rays_unit = ray_unit[..., None, :].expand_as(points).contiguous()
         gradients, hessians = self.neural_sdf.compute_gradients(points, training=self.training, sdf=sdfs)
-        normals = torch_F.normalize(gradients, dim=-1)
-        rgbs = self.neural_rgb.forward(points, normals, rays_unit, feats, app=app)
+        # normals = normalize(gradients); rgbs = neural_rgb(points, normals, rays, feats, app) (model.py:179-183)
+        rgbs = self.neural_rgb.forward_from_gradients(points, gradients, ray_unit, feats, app)
         return dict(rgbs=rgbs, sdfs=sdfs, dists=dists, gradients=gradients, hessians=hessians)
 
     def render_rays_background(self, center, ray_unit, far, app_outside, stratified=False):

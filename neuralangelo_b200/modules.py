@@ -293,13 +293,20 @@ class NeuralSDF(torch.nn.Module):
         if mode != "numerical":
             raise ValueError(mode)
         eps, offsets = self._tap_offsets()
+        taps_sdf = None
         if self._hashgrid() and x.is_cuda and self._planes_supported() and not self._needs_graph() \
                 and not (torch.is_grad_enabled() and x.requires_grad):
-            s = [t.view(*x.shape[:-1], 1) for t in self.sdf_planes(x.reshape(-1, 3), taps=offsets).unbind(0)]
+            taps_sdf = self.sdf_planes(x.reshape(-1, 3), taps=offsets)                # [T,N,1]
         elif self._hashgrid():
             rows = self.encode_rows(x.reshape(-1, 3), taps=offsets)                 # [T,N,3+LD], one encode launch
-            s = self.run_mlp(rows, with_sdf=True, with_feat=False)[0]                # [T,N,1], one MLP pass
-            s = [t.view(*x.shape[:-1], 1) for t in s.unbind(0)]
+            taps_sdf = self.run_mlp(rows, with_sdf=True, with_feat=False)[0]         # [T,N,1], one MLP pass
+        if taps_sdf is not None and x.is_cuda:
+            # gradient / curvature arithmetic as ONE launch per direction (csrc/glue.cu) instead of ~15 + ~30 ATen kernels
+            from . import glue
+            return glue.tap_combine(taps_sdf.view(len(offsets), *x.shape[:-1], 1), sdf, self.cfg_sdf.gradient.taps, eps,
+                                    training)
+        if taps_sdf is not None:
+            s = [t.view(*x.shape[:-1], 1) for t in taps_sdf.unbind(0)]
         else:
             s = [self.sdf(x + torch.tensor(o, dtype=x.dtype, device=x.device)) for o in offsets]
         hessian = None
@@ -378,6 +385,9 @@ class NeuralRGB(torch.nn.Module):
         if self.cfg_rgb.mode == "no_normal":
             input_list = [t for t in input_list if t is not normals]
         input_vec = torch.cat(input_list, dim=-1)
+        return self._run_mlp(input_vec)
+
+    def _run_mlp(self, input_vec):
         if input_vec.is_cuda and _chain_supported(self.mlp):
             # tcgen05 chain kernel (csrc/mlp_chain.cu): all five layers + sigmoid in one launch
             from . import fused_chain
@@ -397,6 +407,20 @@ class NeuralRGB(torch.nn.Module):
         if self.cfg_rgb.encoding_view.type == "spherical":
             return self.spherical_harmonic_encoding(rays_unit)
         raise NotImplementedError("Unknown encoding type")
+
+    def forward_from_gradients(self, points_3D, gradients, ray_unit, feats, app):
+        """forward(points, normalize(gradients), ray_unit broadcast over the samples, feats, app) as the reference's
+        model.py:179-183 calls it, with the input row built by ONE kernel (csrc/glue.cu: SH of the view direction,
+        normalisation and the 278-wide concatenation) where the configuration allows (idr mode, spherical view encoding,
+        CUDA); ray_unit is [B,R,3]."""
+        if self.cfg_rgb.mode == "idr" and self.cfg_rgb.encoding_view.type == "spherical" and feats.is_cuda and \
+                self.cfg_rgb.encoding_view.levels <= 4:
+            from . import glue
+            input_vec = glue.rgb_input(points_3D, ray_unit, gradients, feats, app, self.cfg_rgb.encoding_view.levels)
+            return self._run_mlp(input_vec)
+        normals = F.normalize(gradients, dim=-1)
+        rays_unit = ray_unit[..., None, :].expand_as(points_3D).contiguous()
+        return self.forward(points_3D, normals, rays_unit, feats, app)
 
 
 class BackgroundNeRF(torch.nn.Module):
