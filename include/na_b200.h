@@ -234,7 +234,7 @@ int na_mc_run_static(const float* volume, int nx, int ny, int nz, double iso, do
  * i.e. the bias gradient arrives as column k_in of the same buffer.  `dw` must be ZERO-FILLED by the caller (row slices
  * add their partial sums with vector reductions), 16-byte aligned, ld_w >= k_in + 1 and a multiple of 4.  `amax`: device
  * scalar holding max|dy|; dy is multiplied by 2^floor(log2(4096 / amax)) before its conversion to fp16 and the result
- * divided by it again (NULL = no scaling).  Operands of dW in fp16 (10-bit mantissa, as the TF32 GEMMs the reference
+ * divided by it again (NULL: every CTA takes the maximum over its own row slice in a first sweep).  Operands of dW in fp16 (10-bit mantissa, as the TF32 GEMMs the reference
  * runs), accumulation in fp32; the bias gradient is an fp32 sum of the unconverted dy.  k_in <= 352, any n_out, any m.
  * Replaces: autograd's weight-gradient GEMM + bias-gradient reduction of every nn.Linear on the path
  * (projects/neuralangelo/utils/mlp.py:55-69, projects/nerf/utils/nerf_util.py:186-196). */

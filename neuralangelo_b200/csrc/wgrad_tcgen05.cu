@@ -125,15 +125,29 @@ __global__ void __launch_bounds__(kWgThreads, 2) linear_wgrad_kernel(const __gri
     } else {
         // ===================== staging warps =====================
         // dy is multiplied by 2^floor(log2(4096 / max|dy|)) (max|dy| read from device memory) before its conversion
-        float scale = 1.f;
-        if (P.scale) {
-            const float amax = __ldg(P.scale);
-            if (amax > 0.f && amax < 3.0e38f) scale = exp2f(floorf(log2f(4096.f / amax)));
-        }
         const int t = threadIdx.x;
         const uint32_t b_kstride = (uint32_t)kp / 8 * 128;      // bytes between k-chunks of the B image
         const int ca = t & 127, half = t >> 7;                   // A: column of the tile and which 32 of the 64 rows
         const bool col_ok = n0 + ca < P.n_out;
+        // The largest |dy| comes from the caller (one value for the whole matrix) or, without one, from a first sweep over
+        // this CTA's own slice of dy (its second read comes out of the L2): a CTA's partial sum is scaled back before it
+        // is added to dW, so every CTA may use its own power of two.
+        float amax = 0.f;
+        if (P.scale) {
+            amax = __ldg(P.scale);
+        } else {
+            if (col_ok)
+                for (int64_t r = m0 + half; r < m1; r += 2) amax = fmaxf(amax, fabsf(__ldg(P.dy + r * P.ld_dy + n0 + ca)));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+            __shared__ float red[kStageWarps];
+            if (lane == 0) red[warp] = amax;
+            asm volatile("bar.sync 1, %0;" ::"n"(kStageThreads) : "memory");
+#pragma unroll
+            for (int w = 0; w < kStageWarps; ++w) amax = fmaxf(amax, red[w]);
+        }
+        float scale = 1.f;
+        if (amax > 0.f && amax < 3.0e38f) scale = exp2f(floorf(log2f(4096.f / amax)));
         float bias_acc = 0.f;                                    // fp32 column sum of dy: the bias gradient, exact products
         for (int st = 0; st < n_steps; ++st) {
             const int s = st % kWgStages;
