@@ -47,6 +47,8 @@ class FusedAdamW:
             off += k
         self.n_small = n
         self.small_params = small
+        self._grad_views = [p.grad for p in small]
+        self.gather_mode = False
         self.table = table
         if table is not None:
             self.encoding.accumulate_grad_in_place = True
@@ -59,6 +61,25 @@ class FusedAdamW:
                               for l in range(self.n_levels)]
             self.applied_levels = self.n_levels if not self.lazy else 0  # levels whose decay is up to date
             self.pending_log_decay = 0.0  # log of prod (1 - lr*wd) over the steps skipped by inactive levels
+
+    def use_gathered_grads(self):
+        """Let autograd hand out fresh gradient tensors (`.grad = None` before every backward) and add them into the flat
+        bucket with ONE multi-tensor launch (collect_grads) instead of one AccumulateGrad `add_` per parameter (~50 per
+        step).  The caller runs collect_grads() after every backward."""
+        self.gather_mode = True
+        for p in self.small_params:
+            p.grad = None
+
+    def collect_grads(self):
+        if not self.gather_mode:
+            return
+        views, grads = [], []
+        for v, p in zip(self._grad_views, self.small_params):
+            if p.grad is not None:
+                views.append(v), grads.append(p.grad)
+                p.grad = None
+        if views:
+            torch._foreach_add_(views, grads)
 
     def active_prefix(self):
         """Number of table parameters in active levels (a prefix: levels are stored coarse to fine)."""

@@ -41,6 +41,7 @@ class TrainStep:
         if self.data_parallel:
             parallel.broadcast_parameters([p.data for p in model.parameters()])
         self.optim = FusedAdamW(model, lr=lr, weight_decay=weight_decay)
+        self.optim.use_gathered_grads()
         self.multimem = False
         if self.data_parallel and self.optim.table is not None and self.optim.lazy and table_exchange in ("auto", "multimem"):
             self.multimem = self.optim.enable_multimem()
@@ -126,6 +127,7 @@ class TrainStep:
         out = self.model(data)
         loss = self.compute_loss(out, data["image_sampled"])
         loss.backward()
+        self.optim.collect_grads()     # the small parameters' gradients -> flat bucket, one multi-tensor launch
         return loss
 
     def _schedule_key(self, data):
