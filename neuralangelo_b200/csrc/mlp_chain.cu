@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_fwd_kernel(const __grid
 
     if (warp == kComputeWarps + 1) {
         // ===================== weight loader =====================
-        if (lane == 0) {
+        if (elect_one()) {
             uint32_t it = 0;
             for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 for (int si = 0; si < P.n_stages; ++si) {
@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_fwd_kernel(const __grid
         }
     } else if (warp == kComputeWarps) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        if (elect_one()) {
             const uint32_t a_lbo = kTileM / 8 * 128;
             uint32_t it = 0, gemm_it = 0;
             for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {

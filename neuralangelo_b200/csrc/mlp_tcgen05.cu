@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) sdf_mlp_fwd_kernel(const __gri
 
     if (warp == kFwdWarps + 1) {
         // ===================== weight loader =====================
-        if (lane == 0) {
+        if (elect_one()) {
             uint32_t it = 0;
             for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 for (int l = 0; l < P.n_layers; ++l) {
@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) sdf_mlp_fwd_kernel(const __gri
         }
     } else if (warp == kFwdWarps) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        if (elect_one()) {
             const uint32_t idesc = make_idesc(kTileM, n);
             const uint32_t a_lbo = kTileM / 8 * 128, b_lbo = (uint32_t)n / 8 * 128;
             uint32_t it = 0, layer_it = 0;
@@ -413,7 +413,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) sdf_head_fwd_pipe_kernel(cons
 
     if (warp == kPipeWarps) {
         // ===================== weights (once) + MMA issuer =====================
-        if (lane == 0) {
+        if (elect_one()) {
             mbar_expect_tx(w_full, 2u * w_bytes);
             bulk_copy_g2s(smem_u32(w_hi), P.layer[0].w_hi, w_bytes, w_full);
             bulk_copy_g2s(smem_u32(w_lo), P.layer[0].w_lo, w_bytes, w_full);
@@ -741,7 +741,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_c
 
     if (warp == kComputeWarps + 1) {
         // ===================== weight loader: per tile [W1^T] then W0^T =====================
-        if (lane == 0) {
+        if (elect_one()) {
             uint32_t it = 0;
             for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 for (int g = 0; g < n_mma; ++g) {
@@ -767,7 +767,7 @@ __global__ void __launch_bounds__(kThreads, 1) sdf_mlp_bwd_kernel(const __grid_c
         }
     } else if (warp == kComputeWarps) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        if (elect_one()) {
             const uint32_t a_lbo = kTileM / 8 * 128;
             uint32_t it = 0, mma_it = 0;
             for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {

@@ -12,6 +12,16 @@ constexpr float kLoScale = 2048.f, kLoInv = 1.f / 2048.f;
 // ---------------------------------------------------------------- PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// One lane of a CONVERGED warp.  Use this, not `lane == 0`, to pick the thread that issues tcgen05.mma / commit: ptxas
+// then knows a single thread runs the branch and emits the uniform-datapath instructions back to back; behind a plain
+// lane test it wraps every UTCHMMA in an ELECT / BRA.U.ANY loop over the "possibly many" active lanes and moves each
+// descriptor through R2UR (14 instructions per MMA, more than the 64 cycles a 128x128x16 MMA takes).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+    return pred != 0;
+}
+
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }

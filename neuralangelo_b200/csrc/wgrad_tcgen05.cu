@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(kWgThreads, 2) linear_wgrad_kernel(const __gri
 
     if (warp == kStageWarps) {
         // ===================== MMA issuer =====================
-        if (lane == 0 && n_steps > 0) {
+        if (n_steps > 0 && elect_one()) {
             const int n1 = kp > 256 ? 256 : kp, n2 = kp - n1;      // two column groups when x is wider than 256
             const uint32_t idesc1 = make_idesc(128, n1), idesc2 = n2 ? make_idesc(128, n2) : 0u;
             const uint32_t a_lbo = 128 / 8 * 128, b_lbo = (uint32_t)kp / 8 * 128;

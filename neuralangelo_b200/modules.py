@@ -161,16 +161,35 @@ class NeuralSDF(torch.nn.Module):
         sdf = self._packed_mlp().forward_planes(planes, planes.shape[1])
         return sdf.view(len(taps), points_flat.shape[0], 1)
 
-    def sdf_lattice(self, gx, gy, gz):
+    def _lattice_fused_supported(self):
+        enc, mlp = self.tcnn_encoding, self._packed_mlp()
+        return (mlp is not None and enc.desc.n_levels == 16 and enc.desc.n_features == 8 and mlp.n == 256
+                and mlp.k0 == 131 and mlp.k0_pad == 144)
+
+    def sdf_lattice(self, gx, gy, gz, fused=None):
         """SDF on the lattice gx x gy x gz (float32 CUDA axis arrays, x slowest: one block of extract_mesh) without an
-        [N,3] coordinate tensor: the encode kernel derives each point from the axes and writes the MLP's xyz chunk
-        itself (na_hashgrid_lattice_fwd_strided), then one launch of the pipelined SDF-only MLP.  Returns [nx,ny,nz]."""
+        [N,3] coordinate tensor.  Default shape (16 levels x 8 features, 256-wide MLP): ONE kernel (na_lattice_sdf) that
+        gathers along z runs straight into the tensor-core operand; other shapes (or fused=False): the encode kernel
+        derives each point from the axes and writes the MLP's chunk planes (na_hashgrid_lattice_fwd_strided), then one
+        launch of the pipelined SDF-only MLP.  Returns [nx,ny,nz]."""
         import ctypes
         enc = self.tcnn_encoding
         if not self._planes_supported():
             raise NotImplementedError("sdf_lattice needs the chunk-plane path (8 features per level, fused MLP envelope)")
         nx, ny, nz = gx.numel(), gy.numel(), gz.numel()
         n, n_levels = nx * ny * nz, enc.desc.n_levels
+        if fused is None:
+            fused = self._lattice_fused_supported()
+        if fused:
+            mlp = self._packed_mlp()
+            sdf = torch.empty(nx, ny, nz, dtype=torch.float32, device=gx.device)
+            rc = _lib.lib().na_lattice_sdf(
+                ctypes.byref(enc.desc), _lib.ptr(enc.params.detach()), _lib.ptr(gx), _lib.ptr(gy), _lib.ptr(gz), nx, ny, nz,
+                self._unit_map, int(self._levels_in_use()), _lib.ptr(mlp.w0p_hi), _lib.ptr(mlp.w0p_lo), _lib.ptr(mlp.b0),
+                mlp.k0_pad, mlp.n, _lib.ptr(mlp.w_head), _lib.ptr(mlp.b_head), mlp.beta, _lib.ptr(sdf),
+                _lib.current_stream())
+            _lib.check(rc, "na_lattice_sdf")
+            return sdf
         planes = torch.empty(n_levels + 1, n, 8, dtype=torch.float32, device=gx.device)
         rc = _lib.lib().na_hashgrid_lattice_fwd_strided(
             ctypes.byref(enc.desc), _lib.ptr(enc.params.detach()), _lib.ptr(gx), _lib.ptr(gy), _lib.ptr(gz), nx, ny, nz,

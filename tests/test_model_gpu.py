@@ -390,14 +390,10 @@ def test_default_config_matches_reference(na_lib, cuda_device, golden_dir, taps,
     assert float(tg[zidx].abs().max()) == 0.0
 
 
-def test_lattice_query_and_batched_extraction_match_the_coordinate_path(na_lib, cuda_device):
-    """NeuralSDF.sdf_lattice (axes in, no [N,3] tensor: na_hashgrid_lattice_fwd_strided) is bit-identical to querying the
-    materialised meshgrid, and extract_mesh's batched no-round-trip path returns the same mesh whether sdf_func offers
-    `.lattice` or is a plain callable (mesh.py:24-49, 96-99)."""
-    from neuralangelo_b200 import mesh
+def _lattice_net(cuda_device, active=11, seed=5):
     from neuralangelo_b200.config import default_model_config
     from neuralangelo_b200.modules import NeuralSDF
-    torch.manual_seed(5)
+    torch.manual_seed(seed)
     cfg = default_model_config()
     net = NeuralSDF(cfg.object.sdf).to(cuda_device).eval()
     with torch.no_grad():
@@ -405,16 +401,35 @@ def test_lattice_query_and_batched_extraction_match_the_coordinate_path(na_lib, 
         for lin in net.mlp.linears:
             lin.weight_v.add_(torch.randn_like(lin.weight_v) * 0.02)
     net.warm_up_end = 0
-    net.set_active_levels(current_iter=11 * cfg.object.sdf.encoding.coarse2fine.step)   # 11 of 16 levels
+    net.set_active_levels(current_iter=active * cfg.object.sdf.encoding.coarse2fine.step)
+    return net
+
+
+def test_lattice_query_and_batched_extraction_match_the_coordinate_path(na_lib, cuda_device):
+    """NeuralSDF.sdf_lattice's two-launch form (axes in, no [N,3] tensor: na_hashgrid_lattice_fwd_strided) is bit-identical
+    to querying the materialised meshgrid; the one-kernel form (na_lattice_sdf, the default at this shape) agrees to
+    fp32 rounding; extract_mesh's batched no-round-trip path returns the same mesh whether sdf_func offers `.lattice` or
+    is a plain callable (mesh.py:24-49, 96-99)."""
+    from neuralangelo_b200 import mesh
+    net = _lattice_net(cuda_device)
     gx = torch.linspace(-0.9, 0.7, 37, device=cuda_device)
     gy = torch.linspace(-0.5, 0.8, 21, device=cuda_device)
     gz = torch.linspace(-1.0, 1.0, 45, device=cuda_device)
     with torch.no_grad():
-        lat = net.sdf_lattice(gx, gy, gz)
+        lat = net.sdf_lattice(gx, gy, gz, fused=False)
+        fused = net.sdf_lattice(gx, gy, gz)
         ref = net.sdf(torch.stack(torch.meshgrid(gx, gy, gz, indexing="ij"), dim=-1))[..., 0]
+    assert net._lattice_fused_supported()
     assert lat.shape == (37, 21, 45) and torch.equal(lat, ref)
+    assert fused.shape == (37, 21, 45)
+    assert float((fused - ref).abs().max()) <= 2e-6 * max(1.0, float(ref.abs().max()))   # SDF tolerance: 1e-3 relative
     bounds = np.array([[-1.0, 1.0]] * 3)
-    a = mesh.extract_mesh(mesh.LatticeSDF(net), bounds, intv=2.0 / 80, block_res=32)
+
+    class TwoLaunch(mesh.LatticeSDF):
+        def lattice(self, gx, gy, gz):
+            return self.sign * self.neural_sdf.sdf_lattice(gx, gy, gz, fused=False)
+
+    a = mesh.extract_mesh(TwoLaunch(net), bounds, intv=2.0 / 80, block_res=32)
     b = mesh.extract_mesh(lambda x: -net.sdf(x), bounds, intv=2.0 / 80, block_res=32)
     assert len(a.vertices) > 1000 and np.array_equal(a.vertices, b.vertices) and np.array_equal(a.faces, b.faces)
     assert np.linalg.norm(a.vertices, axis=1).max() < 1.0
@@ -422,3 +437,34 @@ def test_lattice_query_and_batched_extraction_match_the_coordinate_path(na_lib, 
     c = mesh.extract_mesh(lambda x: -net.sdf(x), bounds, intv=2.0 / 80, block_res=32,
                           texture_func=lambda xyz: np.zeros((len(xyz), 3), dtype=np.uint8))
     assert np.array_equal(a.vertices, c.vertices) and np.array_equal(a.faces, c.faces)
+    # one-kernel block query: the same surface (vertex sets within 1e-4 of the bounding-box diagonal of each other)
+    from scipy.spatial import cKDTree
+    f = mesh.extract_mesh(mesh.LatticeSDF(net), bounds, intv=2.0 / 80, block_res=32)
+    assert abs(len(f.vertices) - len(a.vertices)) <= 1e-3 * len(a.vertices) and abs(len(f.faces) - len(a.faces)) <= 1e-3 * len(a.faces)
+    diag = float(np.linalg.norm(bounds[:, 1] - bounds[:, 0]))
+    assert cKDTree(a.vertices).query(f.vertices)[0].max() <= 1e-4 * diag
+    assert cKDTree(f.vertices).query(a.vertices)[0].max() <= 1e-4 * diag
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,active", [((129, 129, 129), 16), ((5, 3, 1), 16), ((16, 16, 8), 4), ((33, 2, 77), 9),
+                                          ((1, 1, 300), 16)])
+def test_one_kernel_lattice_sdf_matches_the_two_launch_path(na_lib, cuda_device, shape, active):
+    """na_lattice_sdf (z-run gather -> tcgen05 operand -> head, one kernel) against encode planes + SDF-only MLP on the same
+    lattice: block shape of extract_mesh (129^3, two lattice points per finest cell as at 2048^3), ragged / tiny lattices,
+    coarse-to-fine masks, a coarse lattice whose z steps jump several fine cells."""
+    net = _lattice_net(cuda_device, active=active, seed=11)
+    nx, ny, nz = shape
+    if shape == (129, 129, 129):      # one block of the 2048^3 extraction: spacing 2 / 2048
+        gx = -0.3 + torch.arange(nx, device=cuda_device, dtype=torch.float32) * (2.0 / 2048)
+        gy = 0.1 + torch.arange(ny, device=cuda_device, dtype=torch.float32) * (2.0 / 2048)
+        gz = -0.9 + torch.arange(nz, device=cuda_device, dtype=torch.float32) * (2.0 / 2048)
+    else:
+        gx = torch.linspace(-1.0, 0.9, nx, device=cuda_device)
+        gy = torch.linspace(-0.7, 1.0, ny, device=cuda_device)
+        gz = torch.linspace(-1.0, 1.0, nz, device=cuda_device)
+    with torch.no_grad():
+        ref = net.sdf_lattice(gx, gy, gz, fused=False)
+        got = net.sdf_lattice(gx, gy, gz, fused=True)
+    assert got.shape == ref.shape and bool(torch.isfinite(got).all())
+    assert float((got - ref).abs().max()) <= 2e-6 * max(1.0, float(ref.abs().max()))
