@@ -130,13 +130,15 @@ int na_hashgrid_lattice_fwd_strided(const na_hashgrid_desc* desc, const float* t
  * applied to [xyz | encode(xyz)] of lattice point (gx[ix], gy[iy], gz[iz]).  The encode is gathered along runs of 8 z
  * neighbours (two bilinear face values + one per cell crossing instead of 8 rows per point) straight into the
  * split-fp16 tcgen05 operand in shared memory: no feature planes in HBM.  Envelope: 16 levels x 8 features, hidden
- * width n = 256, k0_pad = 144; w0_hi / w0_lo / b0 / w_head / b_head as for na_sdf_head_fwd_planes (xyz columns LAST).
+ * width n = 256, k0_pad = 144.  Operands are pre-scaled (PackedSdfMlp.lattice_operands): w0s_hi / w0s_lo = the packed
+ * split-fp16 image (layout of na_sdf_head_fwd_planes, feature columns first) of c * [W0 | b0 | 0 ...] with
+ * c = beta * log2(e) -- column 131 multiplies a constant-one input, i.e. carries the bias; w_head_s = w_head * ln2 / beta.
  * Replaces: LatticeGrid.__getitem__ + sdf_func(xyz) per block, projects/neuralangelo/utils/mesh.py:32-35,68-100
  * (-> NeuralSDF.sdf, utils/modules.py:72-74). */
 int na_lattice_sdf(const na_hashgrid_desc* desc, const float* table, const float* gx, const float* gy,
                    const float* gz, int nx, int ny, int nz, na_unit_map map, uint32_t active_levels,
-                   const void* w0_hi, const void* w0_lo, const float* b0, int k0_pad, int n,
-                   const float* w_head, const float* b_head, float beta, float* sdf_out, void* stream);
+                   const void* w0s_hi, const void* w0s_lo, int k0_pad, int n, const float* w_head_s,
+                   const float* b_head, float* sdf_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * NeuS volume rendering and hierarchical resampling (one warp per ray).

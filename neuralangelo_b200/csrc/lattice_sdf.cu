@@ -10,12 +10,16 @@
 // Warp roles (640 threads, registers re-distributed with setmaxnreg):
 //   warps 0-7    gather: thread = (column, level); features of its 8 points are computed into registers while the
 //                previous tile is still in the tensor pipe, then stored into the A image of its k-chunk group
-//   warps 8-15   epilogue: TMEM -> bias + softplus -> dot with the head row -> SDF
+//   warps 8-15   epilogue: TMEM -> softplus -> dot with the head row -> SDF
 //   warp 16      weights (once, bulk copy) and MMA issue; warps 17-19 only give their registers away
 // The A image is single-buffered (W_hi + W_lo take 144 KB of shared memory), but its four k-chunk groups (4 levels
 // each; the last one also holds the xyz chunk) are released and re-filled one by one: a_free[g] is committed after the
 // LAST pass over group g, a_ready[g] is awaited before the FIRST pass of the next tile over it, so a group's gather
 // warps have three group-times of MMA to store their registers without stalling the tensor pipe.
+// Operands arrive PRE-SCALED so that the epilogue is seven instructions per hidden unit: W0 and b0 are multiplied by
+// beta * log2(e) and b0 is the weight row of a constant-one input column (next to xyz), so the accumulator holds
+// t = beta * log2(e) * (W0 x + b0); softplus_beta(z) * beta / ln 2 = max(t, 0) + log2(1 + 2^-|t|); the head row carries the
+// remaining ln 2 / beta.
 #include "tc_common.cuh"
 
 using namespace na_tc;
@@ -45,14 +49,13 @@ struct Params {
     na_unit_map map;
     uint32_t active_levels;
     const __half *w_hi, *w_lo;
-    const float *bias, *w_head, *b_head;
-    float beta;
+    const float *w_head, *b_head;
     float* sdf_out;
 };
 
 constexpr uint32_t kABytes = kTileM * kKPad * 2;   // one fp16 A image (hi or lo)
 constexpr uint32_t kWBytes = kKPad * kN * 2;
-constexpr uint32_t kSmemBytes = 2 * kABytes + 2 * kWBytes + (2 * 2 * kTileM + 2 * kN) * 4 + kLevels * sizeof(LevelC) +
+constexpr uint32_t kSmemBytes = 2 * kABytes + 2 * kWBytes + (2 * 2 * kTileM + kN) * 4 + kLevels * sizeof(LevelC) +
                                 kBars * 8 + 16;
 
 struct R8 {
@@ -76,6 +79,15 @@ __device__ int na_lattice_dev_mode;
 #define DEV_MODE(bit) false
 #endif
 
+// max(t, 0) + log2(1 + 2^-|t|): softplus in the log2 domain (raw ex2 / lg2: ~1e-7 absolute on the log term, which the
+// head row scales by ln 2 / beta)
+__device__ __forceinline__ float softplus2(float t) {
+    float e, l;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-fabsf(t)));
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(1.f + e));
+    return fmaxf(t, 0.f) + l;
+}
+
 __device__ __noinline__ uint32_t wrap_index(uint32_t idx, uint32_t entries) { return idx % entries; }
 
 template <int REGS>
@@ -94,8 +106,7 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
     uint8_t* w_hi = a_lo + kABytes;
     uint8_t* w_lo = w_hi + kWBytes;
     float* head_partial = reinterpret_cast<float*>(w_lo + kWBytes);   // [2][2][kTileM]
-    float* s_bias = head_partial + 2 * 2 * kTileM;
-    float* s_head = s_bias + kN;
+    float* s_head = head_partial + 2 * 2 * kTileM;
     LevelC* s_lv = reinterpret_cast<LevelC*>(s_head + kN);
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_lv + kLevels);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kBars);
@@ -115,7 +126,6 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
     const int64_t n_tiles = ((n_cols + kCols - 1) / kCols) * n_zr;
 
     for (int i = threadIdx.x; i < kN; i += kThreads) {
-        s_bias[i] = P.bias[i];
         s_head[i] = P.w_head[i];
     }
     if (threadIdx.x < kLevels) {
@@ -285,7 +295,8 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
                     bxy[k] = L.hashed ? (ux ^ (uy * 2654435761u)) : (ux + uy * L.res);
                     w4[k] = ((k & 1) ? wx : 1.f - wx) * ((k >> 1) ? wy : 1.f - wy);
                 }
-                auto face = [&](int cz) {
+                // bilinear (x, y) combination of the four rows of the cell face at height cf
+                auto face_into = [&](R8& f, int cf) {
                     R8 r[4];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
@@ -293,15 +304,16 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
 #pragma unroll
                             for (int e = 0; e < 8; ++e) r[k].v[e] = 0.f;
                         } else {
-                            r[k] = row_load(base + (size_t)row_index(bxy[k], cz) * 8, pol);
+                            r[k] = row_load(base + (size_t)row_index(bxy[k], cf) * 8, pol);
                         }
                     }
-                    R8 f;
 #pragma unroll
                     for (int e = 0; e < 8; ++e)
                         f.v[e] = fmaf(w4[3], r[3].v[e], fmaf(w4[2], r[2].v[e], fmaf(w4[1], r[1].v[e], w4[0] * r[0].v[e])));
-                    return f;
                 };
+                // fa / fb: the faces below / above the current point.  Both are new at the start of the run or after a jump,
+                // one after a step into the next cell.  ONE inlined copy of face_into() per point keeps the unrolled loop
+                // small, and lanes that need a face at the same time share the instructions.
                 R8 fa{}, fb{};
                 int cur = 0;
 #pragma unroll
@@ -309,16 +321,13 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
                     const float pz = fmaf(L.scale, (zs[j] - vmin) * vinv, 0.5f);
                     const float fz = floorf(pz);
                     const int cz = (int)fz;
-                    const float wz = pz - fz;
-                    // faces (cz, cz + 1): both new at the start of the run or after a jump, one new after a step into the
-                    // next cell.  ONE inlined copy of face() per point keeps the unrolled loop inside the instruction cache.
+                    const float wz = pz - fz, uz = 1.f - wz;
                     int need = j == 0 ? 2 : (cz == cur ? 0 : (cz == cur + 1 ? 1 : 2));
                     for (; need > 0; --need) {
                         fa = fb;
-                        fb = face(cz + 2 - need);
+                        face_into(fb, cz + 2 - need);
                     }
                     cur = cz;
-                    const float uz = 1.f - wz;
 #pragma unroll
                     for (int e = 0; e < 4; ++e)
                         split2_f16(fmaf(wz, fb.v[2 * e], uz * fa.v[2 * e]), fmaf(wz, fb.v[2 * e + 1], uz * fa.v[2 * e + 1]),
@@ -344,7 +353,7 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
                 for (int j = 0; j < kRun; ++j) {
                     uint32_t zh, zl;
                     split2_f16(x, y, xh, xl);
-                    split2_f16(zs[j], 0.f, zh, zl);
+                    split2_f16(zs[j], 1.f, zh, zl);   // column 131 = 1: its weight row is the (scaled) bias
                     const uint32_t off = a_chunk_offset(j * kCols + c, kLevels);
                     *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(xh, zh, 0u, 0u);
                     *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(xl, zl, 0u, 0u);
@@ -360,7 +369,6 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
         const int quarter = ew & 3, group = ew >> 2;      // TMEM lane quarter, column half of a unit
         const int row = quarter * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
-        const float beta = P.beta, inv_beta = 1.f / P.beta;
         const float b_head = __ldg(P.b_head);
         float dot = 0.f;
         auto epilogue = [&](int h) {
@@ -375,14 +383,12 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
                 const int gc = h * kNh + c0;
 #pragma unroll
                 for (int j = 0; j < 16; j += 4) {
-                    const float4 b4 = *reinterpret_cast<const float4*>(s_bias + gc + j);
                     const float4 h4 = *reinterpret_cast<const float4*>(s_head + gc + j);
-                    const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w};
+                    const float hh[4] = {h4.x, h4.y, h4.z, h4.w};
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
-                        const float p = fmaf(__uint_as_float(rc[j + e]), kLoInv, __uint_as_float(rm[j + e])) + bb[e];
-                        const float act = (e & 1) ? softplus_poly(p, beta, inv_beta) : softplus(p, beta, inv_beta);
-                        dot = fmaf(act, hh[e], dot);
+                        const float t = fmaf(__uint_as_float(rc[j + e]), kLoInv, __uint_as_float(rm[j + e]));
+                        dot = fmaf(softplus2(t), hh[e], dot);
                     }
                 }
             }
@@ -434,18 +440,17 @@ extern "C" int na_lattice_dev_set(int mode) {
 
 extern "C" int na_lattice_sdf(const na_hashgrid_desc* desc, const float* table, const float* gx, const float* gy,
                               const float* gz, int nx, int ny, int nz, na_unit_map map, uint32_t active_levels,
-                              const void* w0_hi, const void* w0_lo, const float* b0, int k0_pad, int n,
-                              const float* w_head, const float* b_head, float beta, float* sdf_out, void* stream) {
+                              const void* w0s_hi, const void* w0s_lo, int k0_pad, int n, const float* w_head_s,
+                              const float* b_head, float* sdf_out, void* stream) {
     na::clear_error();
-    NA_REQUIRE(desc && table && gx && gy && gz && w0_hi && w0_lo && b0 && w_head && b_head && sdf_out,
+    NA_REQUIRE(desc && table && gx && gy && gz && w0s_hi && w0s_lo && w_head_s && b_head && sdf_out,
                "lattice_sdf: null pointer");
     NA_REQUIRE(nx > 0 && ny > 0 && nz > 0, "lattice_sdf: empty lattice");
     NA_REQUIRE(desc->n_levels == kLevels && desc->n_features == 8,
                "lattice_sdf: %u levels x %u features unsupported (16 x 8)", desc->n_levels, desc->n_features);
     NA_REQUIRE(n == kN && k0_pad == kKPad, "lattice_sdf: hidden width %d / k0_pad %d unsupported (256 / 144)", n, k0_pad);
     NA_REQUIRE(active_levels <= desc->n_levels, "lattice_sdf: active_levels > n_levels");
-    NA_REQUIRE(beta > 0.f, "lattice_sdf: softplus beta must be positive");
-    NA_REQUIRE((uintptr_t)table % 32 == 0 && ((uintptr_t)w0_hi | (uintptr_t)w0_lo) % 16 == 0,
+    NA_REQUIRE((uintptr_t)table % 32 == 0 && ((uintptr_t)w0s_hi | (uintptr_t)w0s_lo) % 16 == 0,
                "lattice_sdf: table must be 32-byte, packed weights 16-byte aligned");
     static int configured[64] = {0};
     int dev = 0;
@@ -467,8 +472,8 @@ extern "C" int na_lattice_sdf(const na_hashgrid_desc* desc, const float* table, 
     P.desc = *desc;
     P.table = table, P.gx = gx, P.gy = gy, P.gz = gz, P.nx = nx, P.ny = ny, P.nz = nz;
     P.map = map, P.active_levels = active_levels;
-    P.w_hi = (const __half*)w0_hi, P.w_lo = (const __half*)w0_lo, P.bias = b0, P.w_head = w_head, P.b_head = b_head;
-    P.beta = beta, P.sdf_out = sdf_out;
+    P.w_hi = (const __half*)w0s_hi, P.w_lo = (const __half*)w0s_lo, P.w_head = w_head_s, P.b_head = b_head;
+    P.sdf_out = sdf_out;
     const int64_t tiles = (((int64_t)nx * ny + kCols - 1) / kCols) * ((nz + kRun - 1) / kRun);
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
     lattice_sdf_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);

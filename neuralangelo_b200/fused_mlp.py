@@ -5,6 +5,8 @@ images the kernel streams into shared memory: W = W_hi + 2^-11 W_lo', K zero-pad
 [K/8][N/8][8][8] (K-chunk-major core matrices).  Packing costs one pass over ~0.1 M weights and is redone
 only when the weights change (once per optimiser step), not per call.
 """
+import math
+
 import torch
 
 from . import _lib
@@ -70,6 +72,7 @@ class PackedSdfMlp:
             new.update(zip(("w1t_hi", "w1t_lo"), pack_weight(w1.detach().float().t().contiguous(), self.n)))
             new["norms"] = torch.stack([w1.detach().abs().sum(dim=0).max().float(),
                                         mlp.linear_sdf.weight.detach().abs().max().float()])
+            new["w0_f32"] = w0.detach().float().contiguous()
             new["b0"] = l0.bias.detach().float().contiguous()
             new["b1"] = l1.bias.detach().float().contiguous()
             new["w_head"] = mlp.linear_sdf.weight.detach().float().reshape(-1).contiguous()
@@ -80,6 +83,27 @@ class PackedSdfMlp:
                     cur.copy_(t)
                 else:
                     setattr(self, name, t.clone())
+        self.epoch = getattr(self, "epoch", 0) + 1
+
+    def lattice_operands(self):
+        """Operands of na_lattice_sdf (packed lazily, once per weight update): (w0s_hi, w0s_lo, w_head_s) with
+        c = beta * log2(e): the split-fp16 image of c * [W0[:, 3:] | W0[:, :3] | b0 | 0 ...] -- the bias rides on a
+        constant-one input column, so the accumulator is the softplus argument in the log2 domain -- and
+        w_head * ln(2) / beta."""
+        if getattr(self, "_lat_epoch", None) != self.epoch:
+            if self.k0 + 1 > self.k0_pad:
+                raise NotImplementedError("no spare input column for the bias")
+            with torch.no_grad():
+                c = self.beta * math.log2(math.e)
+                w = torch.zeros(self.n, self.k0_pad, dtype=torch.float64, device=self.w0_f32.device)
+                w[:, :self.k0 - 3] = self.w0_f32[:, 3:].double() * c
+                w[:, self.k0 - 3:self.k0] = self.w0_f32[:, :3].double() * c
+                w[:, self.k0] = self.b0.double() * c
+                hi, lo = pack_weight(w.float(), self.k0_pad)
+                head = (self.w_head.double() * (math.log(2.0) / self.beta)).float()
+            self._lat = (hi, lo, head)
+            self._lat_epoch = self.epoch
+        return self._lat
 
     def forward(self, rows, with_sdf=True, with_feat=True, with_hidden=False):
         """rows: [M, K0] fp32 CUDA tensor, unit stride in the last dim (row stride free).

@@ -182,12 +182,12 @@ class NeuralSDF(torch.nn.Module):
             fused = self._lattice_fused_supported()
         if fused:
             mlp = self._packed_mlp()
+            w_hi, w_lo, head = mlp.lattice_operands()
             sdf = torch.empty(nx, ny, nz, dtype=torch.float32, device=gx.device)
             rc = _lib.lib().na_lattice_sdf(
                 ctypes.byref(enc.desc), _lib.ptr(enc.params.detach()), _lib.ptr(gx), _lib.ptr(gy), _lib.ptr(gz), nx, ny, nz,
-                self._unit_map, int(self._levels_in_use()), _lib.ptr(mlp.w0p_hi), _lib.ptr(mlp.w0p_lo), _lib.ptr(mlp.b0),
-                mlp.k0_pad, mlp.n, _lib.ptr(mlp.w_head), _lib.ptr(mlp.b_head), mlp.beta, _lib.ptr(sdf),
-                _lib.current_stream())
+                self._unit_map, int(self._levels_in_use()), _lib.ptr(w_hi), _lib.ptr(w_lo), mlp.k0_pad, mlp.n,
+                _lib.ptr(head), _lib.ptr(mlp.b_head), _lib.ptr(sdf), _lib.current_stream())
             _lib.check(rc, "na_lattice_sdf")
             return sdf
         planes = torch.empty(n_levels + 1, n, 8, dtype=torch.float32, device=gx.device)
