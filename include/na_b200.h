@@ -126,7 +126,7 @@ int na_hashgrid_lattice_fwd_strided(const na_hashgrid_desc* desc, const float* t
                                     uint32_t active_levels, float* out, int64_t point_stride, int64_t level_stride,
                                     float* xyz_out, int64_t xyz_stride, void* stream);
 
-/* The whole block query in ONE kernel: sdf_out[(ix*ny + iy)*nz + iz] = SDF head of the one-hidden-layer softplus MLP
+/* The whole block query in ONE kernel: sdf_out[(ix*ny + iy)*nz + iz] = out_scale * SDF head of the one-hidden-layer softplus MLP
  * applied to [xyz | encode(xyz)] of lattice point (gx[ix], gy[iy], gz[iz]).  The encode is gathered along runs of 8 z
  * neighbours (two bilinear face values + one per cell crossing instead of 8 rows per point) straight into the
  * split-fp16 tcgen05 operand in shared memory: no feature planes in HBM.  Envelope: 16 levels x 8 features, hidden
@@ -138,7 +138,7 @@ int na_hashgrid_lattice_fwd_strided(const na_hashgrid_desc* desc, const float* t
 int na_lattice_sdf(const na_hashgrid_desc* desc, const float* table, const float* gx, const float* gy,
                    const float* gz, int nx, int ny, int nz, na_unit_map map, uint32_t active_levels,
                    const void* w0s_hi, const void* w0s_lo, int k0_pad, int n, const float* w_head_s,
-                   const float* b_head, float* sdf_out, void* stream);
+                   const float* b_head, float out_scale, float* sdf_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * NeuS volume rendering and hierarchical resampling (one warp per ray).

@@ -50,6 +50,7 @@ struct Params {
     uint32_t active_levels;
     const __half *w_hi, *w_lo;
     const float *w_head, *b_head;
+    float out_scale;
     float* sdf_out;
 };
 
@@ -417,7 +418,7 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
                 const int zr = (int)(tile % n_zr);
                 const int64_t col = (tile / n_zr) * kCols + oc;
                 const int z = zr * kRun + oz;
-                if (col < n_cols && z < P.nz) P.sdf_out[col * P.nz + z] = b_head + part[r] + part[kTileM + r];
+                if (col < n_cols && z < P.nz) P.sdf_out[col * P.nz + z] = P.out_scale * (b_head + part[r] + part[kTileM + r]);
             }
         }
     }
@@ -441,7 +442,7 @@ extern "C" int na_lattice_dev_set(int mode) {
 extern "C" int na_lattice_sdf(const na_hashgrid_desc* desc, const float* table, const float* gx, const float* gy,
                               const float* gz, int nx, int ny, int nz, na_unit_map map, uint32_t active_levels,
                               const void* w0s_hi, const void* w0s_lo, int k0_pad, int n, const float* w_head_s,
-                              const float* b_head, float* sdf_out, void* stream) {
+                              const float* b_head, float out_scale, float* sdf_out, void* stream) {
     na::clear_error();
     NA_REQUIRE(desc && table && gx && gy && gz && w0s_hi && w0s_lo && w_head_s && b_head && sdf_out,
                "lattice_sdf: null pointer");
@@ -473,7 +474,7 @@ extern "C" int na_lattice_sdf(const na_hashgrid_desc* desc, const float* table, 
     P.table = table, P.gx = gx, P.gy = gy, P.gz = gz, P.nx = nx, P.ny = ny, P.nz = nz;
     P.map = map, P.active_levels = active_levels;
     P.w_hi = (const __half*)w0s_hi, P.w_lo = (const __half*)w0s_lo, P.w_head = w_head_s, P.b_head = b_head;
-    P.sdf_out = sdf_out;
+    P.out_scale = out_scale, P.sdf_out = sdf_out;
     const int64_t tiles = (((int64_t)nx * ny + kCols - 1) / kCols) * ((nz + kRun - 1) / kRun);
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
     lattice_sdf_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);

@@ -85,7 +85,7 @@ class LatticeSDF:
         return self.sign * self.neural_sdf.sdf(xyz)
 
     def lattice(self, gx, gy, gz):
-        return self.sign * self.neural_sdf.sdf_lattice(gx, gy, gz)
+        return self.neural_sdf.sdf_lattice(gx, gy, gz, scale=self.sign)
 
 
 class Mesh:

@@ -166,12 +166,13 @@ class NeuralSDF(torch.nn.Module):
         return (mlp is not None and enc.desc.n_levels == 16 and enc.desc.n_features == 8 and mlp.n == 256
                 and mlp.k0 == 131 and mlp.k0_pad == 144)
 
-    def sdf_lattice(self, gx, gy, gz, fused=None):
+    def sdf_lattice(self, gx, gy, gz, fused=None, scale=1.0):
         """SDF on the lattice gx x gy x gz (float32 CUDA axis arrays, x slowest: one block of extract_mesh) without an
         [N,3] coordinate tensor.  Default shape (16 levels x 8 features, 256-wide MLP): ONE kernel (na_lattice_sdf) that
         gathers along z runs straight into the tensor-core operand; other shapes (or fused=False): the encode kernel
         derives each point from the axes and writes the MLP's chunk planes (na_hashgrid_lattice_fwd_strided), then one
-        launch of the pipelined SDF-only MLP.  Returns [nx,ny,nz]."""
+        launch of the pipelined SDF-only MLP.  Returns scale * sdf as [nx,ny,nz] (scale = -1: the flip of
+        scripts/extract_mesh.py:85, applied in the kernel's last store)."""
         import ctypes
         enc = self.tcnn_encoding
         if not self._planes_supported():
@@ -187,7 +188,7 @@ class NeuralSDF(torch.nn.Module):
             rc = _lib.lib().na_lattice_sdf(
                 ctypes.byref(enc.desc), _lib.ptr(enc.params.detach()), _lib.ptr(gx), _lib.ptr(gy), _lib.ptr(gz), nx, ny, nz,
                 self._unit_map, int(self._levels_in_use()), _lib.ptr(w_hi), _lib.ptr(w_lo), mlp.k0_pad, mlp.n,
-                _lib.ptr(head), _lib.ptr(mlp.b_head), _lib.ptr(sdf), _lib.current_stream())
+                _lib.ptr(head), _lib.ptr(mlp.b_head), float(scale), _lib.ptr(sdf), _lib.current_stream())
             _lib.check(rc, "na_lattice_sdf")
             return sdf
         planes = torch.empty(n_levels + 1, n, 8, dtype=torch.float32, device=gx.device)
@@ -196,7 +197,8 @@ class NeuralSDF(torch.nn.Module):
             self._unit_map, int(self._levels_in_use()), _lib.ptr(planes), 8, n * 8, _lib.ptr(planes[n_levels]), 8,
             _lib.current_stream())
         _lib.check(rc, "na_hashgrid_lattice_fwd_strided")
-        return self._packed_mlp().forward_planes(planes, n).view(nx, ny, nz)
+        sdf = self._packed_mlp().forward_planes(planes, n).view(nx, ny, nz)
+        return sdf if scale == 1.0 else sdf * scale
 
     def _needs_graph(self):
         return torch.is_grad_enabled() and (self.tcnn_encoding.params.requires_grad

@@ -427,7 +427,7 @@ def test_lattice_query_and_batched_extraction_match_the_coordinate_path(na_lib, 
 
     class TwoLaunch(mesh.LatticeSDF):
         def lattice(self, gx, gy, gz):
-            return self.sign * self.neural_sdf.sdf_lattice(gx, gy, gz, fused=False)
+            return self.neural_sdf.sdf_lattice(gx, gy, gz, fused=False, scale=self.sign)
 
     a = mesh.extract_mesh(TwoLaunch(net), bounds, intv=2.0 / 80, block_res=32)
     b = mesh.extract_mesh(lambda x: -net.sdf(x), bounds, intv=2.0 / 80, block_res=32)
