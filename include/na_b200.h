@@ -140,6 +140,15 @@ int na_lattice_sdf(const na_hashgrid_desc* desc, const float* table, const float
                    const void* w0s_hi, const void* w0s_lo, int k0_pad, int n, const float* w_head_s,
                    const float* b_head, float out_scale, float* sdf_out, void* stream);
 
+/* The same warp-specialised pipeline (loader warps -> tcgen05 -> epilogue warps, operands pre-scaled as above) for rows
+ * that already exist: sdf_out[r] = out_scale * SDF head, r < m, from chunk planes [chunk][row][8] (planes != NULL: 16
+ * level chunks + the xyz chunk, chunk_stride floats apart) or from [m, 131] rows with stride ldx (x != NULL, xyz first).
+ * Exactly one of planes / x.  Envelope: 16 levels x 8 features + xyz, n = 256, k0_pad = 144.
+ * Replaces: NeuralSDF.sdf for the finite-difference taps / sampler evaluations, utils/modules.py:72-74,132-156. */
+int na_sdf_head_ws(const float* planes, int64_t chunk_stride, const float* x, int64_t ldx, int64_t m,
+                   const void* w0s_hi, const void* w0s_lo, int k0_pad, int n, const float* w_head_s,
+                   const float* b_head, float out_scale, float* sdf_out, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * NeuS volume rendering and hierarchical resampling (one warp per ray).
  * All tensors fp32 contiguous, [n_rays, n_samples(, k)].  `dist_far` is [n_rays] or NULL (= 1e10,

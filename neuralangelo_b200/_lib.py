@@ -71,6 +71,8 @@ def _declare(lib):
                                                            UnitMap, u32, vp, i64, i64, vp, i64, vp]),
         "na_lattice_sdf": (ctypes.c_int, [descp, vp, vp, vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, UnitMap, u32,
                                           vp, vp, ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_float, vp, vp]),
+        "na_sdf_head_ws": (ctypes.c_int, [vp, i64, vp, i64, i64, vp, vp, ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_float,
+                                          vp, vp]),
         "na_alpha_weights_fwd": (ctypes.c_int, [vp, i64, ctypes.c_int, vp, vp]),
         "na_alpha_weights_bwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, vp, vp]),
         "na_composite_fwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp]),

@@ -35,6 +35,7 @@ constexpr int kN = 256, kNh = 128;
 constexpr int kKPad = 144, kChunks = kKPad / 8;       // 16 levels + xyz chunk + zero chunk
 constexpr int kRegsGather = 136, kRegsEpi = 88, kRegsMma = 32;
 constexpr int kBars = 13;
+constexpr int kSrcLattice = 0, kSrcPlanes = 1, kSrcRows = 2;   // where a tile's 128 input rows come from
 
 struct LevelC {
     float scale;
@@ -51,6 +52,11 @@ struct Params {
     const __half *w_hi, *w_lo;
     const float *w_head, *b_head;
     float out_scale;
+    // row sources of the plain SDF-only MLP (kSrcPlanes / kSrcRows): the same pipeline without the gather
+    const float* planes;
+    int64_t chunk_stride;
+    const float* x;
+    int64_t ldx, m;
     float* sdf_out;
 };
 
@@ -100,6 +106,7 @@ __device__ __forceinline__ void regs_dec() {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS));
 }
 
+template <int SRC>
 __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_constant__ Params P) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* a_hi = smem;
@@ -122,14 +129,14 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
     const int dev_mode = na_lattice_dev_mode;
 #endif
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_zr = (P.nz + kRun - 1) / kRun;
+    const int n_zr = SRC == kSrcLattice ? (P.nz + kRun - 1) / kRun : 1;
     const int64_t n_cols = (int64_t)P.nx * P.ny;
-    const int64_t n_tiles = ((n_cols + kCols - 1) / kCols) * n_zr;
+    const int64_t n_tiles = SRC == kSrcLattice ? ((n_cols + kCols - 1) / kCols) * n_zr : (P.m + kTileM - 1) / kTileM;
 
     for (int i = threadIdx.x; i < kN; i += kThreads) {
         s_head[i] = P.w_head[i];
     }
-    if (threadIdx.x < kLevels) {
+    if (SRC == kSrcLattice && threadIdx.x < kLevels) {
         const int l = threadIdx.x;
         LevelC v;
         v.scale = P.desc.scale[l];
@@ -218,11 +225,6 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
         const int gt = threadIdx.x;
         const int g = gt >> 6, lvl = 4 * g + ((gt & 63) >> 4), c = gt & 15;
         const bool xyz_writer = (gt & 63) < 16 && g == kGroups - 1;
-        const LevelC L = s_lv[lvl];
-        const float* base = P.table + (size_t)L.offset * 8;
-        const bool active = (uint32_t)lvl < P.active_levels;
-        const float vmin = P.map.vol_min, vinv = P.map.inv_extent;
-        const uint64_t pol = na::policy_evict_last();
         if (xyz_writer) {   // the zero chunk after xyz is written once
 #pragma unroll
             for (int j = 0; j < kRun; ++j) {
@@ -231,137 +233,203 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
                 *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(0u, 0u, 0u, 0u);
             }
         }
-        // tcnn grid_index(): dense stride walk or the coherent prime hash, then modulo the level size -- a mask for the
-        // power-of-two hashed levels, otherwise only the wrap-around at the far faces (out of line: a division is ~25
-        // instructions and this lambda is inlined once per point of the unrolled run)
-        auto row_index = [&](uint32_t bxy, int cz) {
-            uint32_t idx = L.hashed ? (bxy ^ ((uint32_t)cz * 805459861u)) : (bxy + (uint32_t)cz * L.zmul);
-            if (L.mask) idx &= L.mask;
-            else if (idx >= L.entries) idx = wrap_index(idx, L.entries);
-            return idx;
-        };
-        // Every row the thread will need for tile t, requested into the L2 a whole tile ahead (no registers held): the
-        // dependent face loads of a run then pay L2-hit latency, not DRAM latency.
-        auto prefetch_tile = [&](int64_t t) {
-            if (t >= n_tiles || !active || !DEV_MODE(4)) return;
-            const int64_t pc = (t / n_zr) * kCols + c;
-            if (pc >= n_cols) return;
-            const int pz0 = (int)(t % n_zr) * kRun;
-            const int pix = (int)(pc / P.ny), piy = (int)(pc - (int64_t)pix * P.ny);
-            const float px = fmaf(L.scale, (__ldg(P.gx + pix) - vmin) * vinv, 0.5f);
-            const float py = fmaf(L.scale, (__ldg(P.gy + piy) - vmin) * vinv, 0.5f);
-            const float za = fmaf(L.scale, (__ldg(P.gz + pz0) - vmin) * vinv, 0.5f);
-            const float zb = fmaf(L.scale, (__ldg(P.gz + min(pz0 + kRun - 1, P.nz - 1)) - vmin) * vinv, 0.5f);
-            const uint32_t cx = (uint32_t)(int)floorf(px), cy = (uint32_t)(int)floorf(py);
-            const int ca = (int)floorf(fminf(za, zb)), cb = min((int)floorf(fmaxf(za, zb)) + 1, ca + 11);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint32_t ux = cx + (k & 1), uy = cy + (k >> 1);
-                const uint32_t b = L.hashed ? (ux ^ (uy * 2654435761u)) : (ux + uy * L.res);
-                for (int cz = ca; cz <= cb; ++cz)
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(base + (size_t)row_index(b, cz) * 8));
-            }
-        };
-        prefetch_tile(blockIdx.x);
-        uint32_t q = 0;
-        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
-            if (DEV_MODE(8)) {
-                if (q > 0) mbar_wait(a_free(g), (q - 1) & 1);
-                fence_proxy_async();
-                mbar_arrive(a_ready(g));
-                continue;
-            }
-            prefetch_tile(tile + gridDim.x);
-            const int zr = (int)(tile % n_zr);
-            const int64_t col = (tile / n_zr) * kCols + c;
-            const int z0 = zr * kRun;
-            const bool col_ok = col < n_cols;
-            const int ix = col_ok ? (int)(col / P.ny) : 0, iy = col_ok ? (int)(col - (int64_t)ix * P.ny) : 0;
-            const float x = __ldg(P.gx + ix), y = __ldg(P.gy + iy);
-            float zs[kRun];
-#pragma unroll
-            for (int j = 0; j < kRun; ++j) zs[j] = __ldg(P.gz + min(z0 + j, P.nz - 1));
-
-            uint32_t hi[kRun][4], lo[kRun][4];
-            if (active && col_ok) {
-                const float px = fmaf(L.scale, (x - vmin) * vinv, 0.5f), py = fmaf(L.scale, (y - vmin) * vinv, 0.5f);
-                const float fx = floorf(px), fy = floorf(py);
-                const uint32_t cx = (uint32_t)(int)fx, cy = (uint32_t)(int)fy;
-                const float wx = px - fx, wy = py - fy;
-                uint32_t bxy[4];
-                float w4[4];
-#pragma unroll
+        if constexpr (SRC == kSrcLattice) {
+            const LevelC L = s_lv[lvl];
+            const float* base = P.table + (size_t)L.offset * 8;
+            const bool active = (uint32_t)lvl < P.active_levels;
+            const float vmin = P.map.vol_min, vinv = P.map.inv_extent;
+            const uint64_t pol = na::policy_evict_last();
+            // tcnn grid_index(): dense stride walk or the coherent prime hash, then modulo the level size -- a mask for the
+            // power-of-two hashed levels, otherwise only the wrap-around at the far faces (out of line: a division is ~25
+            // instructions and this lambda is inlined once per point of the unrolled run)
+            auto row_index = [&](uint32_t bxy, int cz) {
+                uint32_t idx = L.hashed ? (bxy ^ ((uint32_t)cz * 805459861u)) : (bxy + (uint32_t)cz * L.zmul);
+                if (L.mask) idx &= L.mask;
+                else if (idx >= L.entries) idx = wrap_index(idx, L.entries);
+                return idx;
+            };
+            // Every row the thread will need for tile t, requested into the L2 a whole tile ahead (no registers held): the
+            // dependent face loads of a run then pay L2-hit latency, not DRAM latency.
+            auto prefetch_tile = [&](int64_t t) {
+                if (t >= n_tiles || !active || !DEV_MODE(4)) return;
+                const int64_t pc = (t / n_zr) * kCols + c;
+                if (pc >= n_cols) return;
+                const int pz0 = (int)(t % n_zr) * kRun;
+                const int pix = (int)(pc / P.ny), piy = (int)(pc - (int64_t)pix * P.ny);
+                const float px = fmaf(L.scale, (__ldg(P.gx + pix) - vmin) * vinv, 0.5f);
+                const float py = fmaf(L.scale, (__ldg(P.gy + piy) - vmin) * vinv, 0.5f);
+                const float za = fmaf(L.scale, (__ldg(P.gz + pz0) - vmin) * vinv, 0.5f);
+                const float zb = fmaf(L.scale, (__ldg(P.gz + min(pz0 + kRun - 1, P.nz - 1)) - vmin) * vinv, 0.5f);
+                const uint32_t cx = (uint32_t)(int)floorf(px), cy = (uint32_t)(int)floorf(py);
+                const int ca = (int)floorf(fminf(za, zb)), cb = min((int)floorf(fmaxf(za, zb)) + 1, ca + 11);
+    #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const uint32_t ux = cx + (k & 1), uy = cy + (k >> 1);
-                    bxy[k] = L.hashed ? (ux ^ (uy * 2654435761u)) : (ux + uy * L.res);
-                    w4[k] = ((k & 1) ? wx : 1.f - wx) * ((k >> 1) ? wy : 1.f - wy);
+                    const uint32_t b = L.hashed ? (ux ^ (uy * 2654435761u)) : (ux + uy * L.res);
+                    for (int cz = ca; cz <= cb; ++cz)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(base + (size_t)row_index(b, cz) * 8));
                 }
-                // bilinear (x, y) combination of the four rows of the cell face at height cf
-                auto face_into = [&](R8& f, int cf) {
-                    R8 r[4];
-#pragma unroll
+            };
+            prefetch_tile(blockIdx.x);
+
+    uint32_t q = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
+                if (DEV_MODE(8)) {
+                    if (q > 0) mbar_wait(a_free(g), (q - 1) & 1);
+                    fence_proxy_async();
+                    mbar_arrive(a_ready(g));
+                    continue;
+                }
+                prefetch_tile(tile + gridDim.x);
+                const int zr = (int)(tile % n_zr);
+                const int64_t col = (tile / n_zr) * kCols + c;
+                const int z0 = zr * kRun;
+                const bool col_ok = col < n_cols;
+                const int ix = col_ok ? (int)(col / P.ny) : 0, iy = col_ok ? (int)(col - (int64_t)ix * P.ny) : 0;
+                const float x = __ldg(P.gx + ix), y = __ldg(P.gy + iy);
+                float zs[kRun];
+    #pragma unroll
+                for (int j = 0; j < kRun; ++j) zs[j] = __ldg(P.gz + min(z0 + j, P.nz - 1));
+
+                uint32_t hi[kRun][4], lo[kRun][4];
+                if (active && col_ok) {
+                    const float px = fmaf(L.scale, (x - vmin) * vinv, 0.5f), py = fmaf(L.scale, (y - vmin) * vinv, 0.5f);
+                    const float fx = floorf(px), fy = floorf(py);
+                    const uint32_t cx = (uint32_t)(int)fx, cy = (uint32_t)(int)fy;
+                    const float wx = px - fx, wy = py - fy;
+                    uint32_t bxy[4];
+                    float w4[4];
+    #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        if (DEV_MODE(1)) {
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) r[k].v[e] = 0.f;
-                        } else {
-                            r[k] = row_load(base + (size_t)row_index(bxy[k], cf) * 8, pol);
-                        }
+                        const uint32_t ux = cx + (k & 1), uy = cy + (k >> 1);
+                        bxy[k] = L.hashed ? (ux ^ (uy * 2654435761u)) : (ux + uy * L.res);
+                        w4[k] = ((k & 1) ? wx : 1.f - wx) * ((k >> 1) ? wy : 1.f - wy);
                     }
-#pragma unroll
-                    for (int e = 0; e < 8; ++e)
-                        f.v[e] = fmaf(w4[3], r[3].v[e], fmaf(w4[2], r[2].v[e], fmaf(w4[1], r[1].v[e], w4[0] * r[0].v[e])));
-                };
-                // fa / fb: the faces below / above the current point.  Both are new at the start of the run or after a jump,
-                // one after a step into the next cell.  ONE inlined copy of face_into() per point keeps the unrolled loop
-                // small, and lanes that need a face at the same time share the instructions.
-                R8 fa{}, fb{};
-                int cur = 0;
+                    // bilinear (x, y) combination of the four rows of the cell face at height cf
+                    auto face_into = [&](R8& f, int cf) {
+                        R8 r[4];
+    #pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            if (DEV_MODE(1)) {
+    #pragma unroll
+                                for (int e = 0; e < 8; ++e) r[k].v[e] = 0.f;
+                            } else {
+                                r[k] = row_load(base + (size_t)row_index(bxy[k], cf) * 8, pol);
+                            }
+                        }
+    #pragma unroll
+                        for (int e = 0; e < 8; ++e)
+                            f.v[e] = fmaf(w4[3], r[3].v[e], fmaf(w4[2], r[2].v[e], fmaf(w4[1], r[1].v[e], w4[0] * r[0].v[e])));
+                    };
+                    // fa / fb: the faces below / above the current point.  Both are new at the start of the run or after a jump,
+                    // one after a step into the next cell.  ONE inlined copy of face_into() per point keeps the unrolled loop
+                    // small, and lanes that need a face at the same time share the instructions.
+                    R8 fa{}, fb{};
+                    int cur = 0;
+    #pragma unroll
+                    for (int j = 0; j < kRun; ++j) {
+                        const float pz = fmaf(L.scale, (zs[j] - vmin) * vinv, 0.5f);
+                        const float fz = floorf(pz);
+                        const int cz = (int)fz;
+                        const float wz = pz - fz, uz = 1.f - wz;
+                        int need = j == 0 ? 2 : (cz == cur ? 0 : (cz == cur + 1 ? 1 : 2));
+                        for (; need > 0; --need) {
+                            fa = fb;
+                            face_into(fb, cz + 2 - need);
+                        }
+                        cur = cz;
+    #pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            split2_f16(fmaf(wz, fb.v[2 * e], uz * fa.v[2 * e]), fmaf(wz, fb.v[2 * e + 1], uz * fa.v[2 * e + 1]),
+                                       hi[j][e], lo[j][e]);
+                    }
+                } else {
+    #pragma unroll
+                    for (int j = 0; j < kRun; ++j)
+    #pragma unroll
+                        for (int e = 0; e < 4; ++e) hi[j][e] = 0u, lo[j][e] = 0u;
+                }
+
+                if (q > 0) mbar_wait(a_free(g), (q - 1) & 1);   // every MMA of the previous tile over this group is done
+    #pragma unroll
+                for (int j = 0; j < kRun; ++j) {
+                    const uint32_t off = a_chunk_offset(j * kCols + c, lvl);
+                    *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[j][0], hi[j][1], hi[j][2], hi[j][3]);
+                    *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[j][0], lo[j][1], lo[j][2], lo[j][3]);
+                }
+                if (xyz_writer) {
+                    uint32_t xh, xl;
+    #pragma unroll
+                    for (int j = 0; j < kRun; ++j) {
+                        uint32_t zh, zl;
+                        split2_f16(x, y, xh, xl);
+                        split2_f16(zs[j], 1.f, zh, zl);   // column 131 = 1: its weight row is the (scaled) bias
+                        const uint32_t off = a_chunk_offset(j * kCols + c, kLevels);
+                        *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(xh, zh, 0u, 0u);
+                        *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(xl, zl, 0u, 0u);
+                    }
+                }
+                fence_proxy_async();
+                mbar_arrive(a_ready(g));
+            }
+        } else {
+            // ---- plain rows: thread = (row mod 16, k-chunk); its 8 rows are 16 apart, so a load instruction of the 16
+            //      lanes of a chunk covers 16 consecutive rows
+            uint32_t q = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++q) {
+                const int64_t r0 = tile * kTileM + c;
+                float v[kRun][8];
+                float xyz[kRun][3];
 #pragma unroll
                 for (int j = 0; j < kRun; ++j) {
-                    const float pz = fmaf(L.scale, (zs[j] - vmin) * vinv, 0.5f);
-                    const float fz = floorf(pz);
-                    const int cz = (int)fz;
-                    const float wz = pz - fz, uz = 1.f - wz;
-                    int need = j == 0 ? 2 : (cz == cur ? 0 : (cz == cur + 1 ? 1 : 2));
-                    for (; need > 0; --need) {
-                        fa = fb;
-                        face_into(fb, cz + 2 - need);
-                    }
-                    cur = cz;
+                    const int64_t gr = r0 + j * kCols;
+                    const bool ok = gr < P.m;
+                    if constexpr (SRC == kSrcPlanes) {
+                        const float* src = P.planes + (int64_t)lvl * P.chunk_stride + gr * 8;
+                        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                        const float4 a = ok ? na::ld_stream_f4(src) : z4, b = ok ? na::ld_stream_f4(src + 4) : z4;
+                        v[j][0] = a.x, v[j][1] = a.y, v[j][2] = a.z, v[j][3] = a.w;
+                        v[j][4] = b.x, v[j][5] = b.y, v[j][6] = b.z, v[j][7] = b.w;
+                        if (xyz_writer) {
+                            const float4 t = ok ? na::ld_stream_f4(P.planes + (int64_t)kLevels * P.chunk_stride + gr * 8) : z4;
+                            xyz[j][0] = t.x, xyz[j][1] = t.y, xyz[j][2] = t.z;
+                        }
+                    } else {
+                        const float* src = P.x + gr * P.ldx;
 #pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                        split2_f16(fmaf(wz, fb.v[2 * e], uz * fa.v[2 * e]), fmaf(wz, fb.v[2 * e + 1], uz * fa.v[2 * e + 1]),
-                                   hi[j][e], lo[j][e]);
+                        for (int e = 0; e < 8; ++e) v[j][e] = ok ? __ldg(src + 3 + 8 * lvl + e) : 0.f;
+                        if (xyz_writer) {
+#pragma unroll
+                            for (int e = 0; e < 3; ++e) xyz[j][e] = ok ? __ldg(src + e) : 0.f;
+                        }
+                    }
                 }
-            } else {
+                uint32_t hi[kRun][4], lo[kRun][4];
 #pragma unroll
                 for (int j = 0; j < kRun; ++j)
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) hi[j][e] = 0u, lo[j][e] = 0u;
-            }
-
-            if (q > 0) mbar_wait(a_free(g), (q - 1) & 1);   // every MMA of the previous tile over this group is done
-#pragma unroll
-            for (int j = 0; j < kRun; ++j) {
-                const uint32_t off = a_chunk_offset(j * kCols + c, lvl);
-                *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[j][0], hi[j][1], hi[j][2], hi[j][3]);
-                *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[j][0], lo[j][1], lo[j][2], lo[j][3]);
-            }
-            if (xyz_writer) {
-                uint32_t xh, xl;
+                    for (int e = 0; e < 4; ++e) split2_f16(v[j][2 * e], v[j][2 * e + 1], hi[j][e], lo[j][e]);
+                if (q > 0) mbar_wait(a_free(g), (q - 1) & 1);
 #pragma unroll
                 for (int j = 0; j < kRun; ++j) {
-                    uint32_t zh, zl;
-                    split2_f16(x, y, xh, xl);
-                    split2_f16(zs[j], 1.f, zh, zl);   // column 131 = 1: its weight row is the (scaled) bias
-                    const uint32_t off = a_chunk_offset(j * kCols + c, kLevels);
-                    *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(xh, zh, 0u, 0u);
-                    *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(xl, zl, 0u, 0u);
+                    const uint32_t off = a_chunk_offset(j * kCols + c, lvl);
+                    *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[j][0], hi[j][1], hi[j][2], hi[j][3]);
+                    *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[j][0], lo[j][1], lo[j][2], lo[j][3]);
                 }
+                if (xyz_writer) {
+#pragma unroll
+                    for (int j = 0; j < kRun; ++j) {
+                        uint32_t xh, xl, zh, zl;
+                        split2_f16(xyz[j][0], xyz[j][1], xh, xl);
+                        split2_f16(xyz[j][2], 1.f, zh, zl);
+                        const uint32_t off = a_chunk_offset(j * kCols + c, kLevels);
+                        *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(xh, zh, 0u, 0u);
+                        *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(xl, zl, 0u, 0u);
+                    }
+                }
+                fence_proxy_async();
+                mbar_arrive(a_ready(g));
             }
-            fence_proxy_async();
-            mbar_arrive(a_ready(g));
         }
     } else {
         regs_dec<kRegsEpi>();
@@ -413,12 +481,17 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
                 asm volatile("bar.arrive %0, %1;" ::"r"(bar_id), "n"(kEpiThreads) : "memory");
             } else {
                 asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(kEpiThreads) : "memory");
-                // A-image row r = zi * 16 + column; thread t writes column t >> 3, z t & 7: 8 consecutive floats per column
-                const int oc = row >> 3, oz = row & 7, r = oz * kCols + oc;
-                const int zr = (int)(tile % n_zr);
-                const int64_t col = (tile / n_zr) * kCols + oc;
-                const int z = zr * kRun + oz;
-                if (col < n_cols && z < P.nz) P.sdf_out[col * P.nz + z] = P.out_scale * (b_head + part[r] + part[kTileM + r]);
+                if constexpr (SRC == kSrcLattice) {
+                    // A-image row r = zi * 16 + column; thread t writes column t >> 3, z t & 7: 8 consecutive floats per column
+                    const int oc = row >> 3, oz = row & 7, r = oz * kCols + oc;
+                    const int zr = (int)(tile % n_zr);
+                    const int64_t col = (tile / n_zr) * kCols + oc;
+                    const int z = zr * kRun + oz;
+                    if (col < n_cols && z < P.nz) P.sdf_out[col * P.nz + z] = P.out_scale * (b_head + part[r] + part[kTileM + r]);
+                } else {
+                    const int64_t gr = tile * kTileM + row;
+                    if (gr < P.m) P.sdf_out[gr] = P.out_scale * (b_head + part[row] + part[kTileM + row]);
+                }
             }
         }
     }
@@ -431,6 +504,29 @@ __global__ void __launch_bounds__(kThreads, 1) lattice_sdf_kernel(const __grid_c
     }
 }
 
+}  // namespace
+
+namespace {
+// once per device and instantiation: shared-memory opt-in, and the register plan checked against the launch allocation
+// (setmaxnreg.inc waits for registers that must exist inside the CTA's launch-time allocation)
+template <int SRC>
+int configure() {
+    static int configured[64] = {0};
+    int dev = 0;
+    if (int rc = na::check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return rc;
+    if (dev >= 64 || configured[dev]) return NA_OK;
+    cudaFuncAttributes attr;
+    if (int rc = na::check_cuda(cudaFuncGetAttributes(&attr, (const void*)lattice_sdf_kernel<SRC>), "cudaFuncGetAttributes"))
+        return rc;
+    NA_REQUIRE(attr.numRegs * kThreads >= kRegsGather * kGatherThreads + kRegsEpi * kEpiThreads + kRegsMma * 128,
+               "lattice_sdf: register plan does not fit (%d registers per thread at launch)", attr.numRegs);
+    if (int rc = na::check_cuda(cudaFuncSetAttribute((const void*)lattice_sdf_kernel<SRC>,
+                                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes),
+                                "cudaFuncSetAttribute(lattice_sdf_kernel)"))
+        return rc;
+    configured[dev] = 1;
+    return NA_OK;
+}
 }  // namespace
 
 #ifdef NA_LATTICE_DEV
@@ -453,22 +549,7 @@ extern "C" int na_lattice_sdf(const na_hashgrid_desc* desc, const float* table, 
     NA_REQUIRE(active_levels <= desc->n_levels, "lattice_sdf: active_levels > n_levels");
     NA_REQUIRE((uintptr_t)table % 32 == 0 && ((uintptr_t)w0s_hi | (uintptr_t)w0s_lo) % 16 == 0,
                "lattice_sdf: table must be 32-byte, packed weights 16-byte aligned");
-    static int configured[64] = {0};
-    int dev = 0;
-    if (int rc = na::check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return rc;
-    if (dev < 64 && !configured[dev]) {
-        cudaFuncAttributes attr;
-        if (int rc = na::check_cuda(cudaFuncGetAttributes(&attr, (const void*)lattice_sdf_kernel), "cudaFuncGetAttributes"))
-            return rc;
-        // setmaxnreg.inc waits for registers that must exist inside the CTA's launch-time allocation
-        NA_REQUIRE(attr.numRegs * kThreads >= kRegsGather * kGatherThreads + kRegsEpi * kEpiThreads + kRegsMma * 128,
-                   "lattice_sdf: register plan does not fit (%d registers per thread at launch)", attr.numRegs);
-        if (int rc = na::check_cuda(cudaFuncSetAttribute((const void*)lattice_sdf_kernel,
-                                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes),
-                                    "cudaFuncSetAttribute(lattice_sdf_kernel)"))
-            return rc;
-        configured[dev] = 1;
-    }
+    if (int rc = configure<kSrcLattice>()) return rc;
     Params P{};
     P.desc = *desc;
     P.table = table, P.gx = gx, P.gy = gy, P.gz = gz, P.nx = nx, P.ny = ny, P.nz = nz;
@@ -477,7 +558,41 @@ extern "C" int na_lattice_sdf(const na_hashgrid_desc* desc, const float* table, 
     P.out_scale = out_scale, P.sdf_out = sdf_out;
     const int64_t tiles = (((int64_t)nx * ny + kCols - 1) / kCols) * ((nz + kRun - 1) / kRun);
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
-    lattice_sdf_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);
+    lattice_sdf_kernel<kSrcLattice><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);
     NA_CHECK_LAUNCH("lattice_sdf_kernel");
+    return NA_OK;
+}
+
+// The same pipeline fed from rows that already exist: chunk planes [chunk][row][8] (planes != NULL) or [m, 131] rows
+// (x != NULL, xyz first as the reference's cat([points, feats])).  Operands as for na_lattice_sdf.
+extern "C" int na_sdf_head_ws(const float* planes, int64_t chunk_stride, const float* x, int64_t ldx, int64_t m,
+                              const void* w0s_hi, const void* w0s_lo, int k0_pad, int n, const float* w_head_s,
+                              const float* b_head, float out_scale, float* sdf_out, void* stream) {
+    na::clear_error();
+    NA_REQUIRE(m >= 0, "sdf_head_ws: negative row count");
+    if (m == 0) return NA_OK;
+    NA_REQUIRE((planes != nullptr) != (x != nullptr), "sdf_head_ws: exactly one of planes / x");
+    NA_REQUIRE(w0s_hi && w0s_lo && w_head_s && b_head && sdf_out, "sdf_head_ws: null pointer");
+    NA_REQUIRE(n == kN && k0_pad == kKPad, "sdf_head_ws: hidden width %d / k0_pad %d unsupported (256 / 144)", n, k0_pad);
+    NA_REQUIRE(((uintptr_t)w0s_hi | (uintptr_t)w0s_lo) % 16 == 0, "sdf_head_ws: packed weights must be 16-byte aligned");
+    if (planes)
+        NA_REQUIRE((uintptr_t)planes % 16 == 0 && chunk_stride % 4 == 0 && chunk_stride >= m * 8,
+                   "sdf_head_ws: planes must be 16-byte aligned with chunk_stride a multiple of 4 and >= 8 m");
+    else
+        NA_REQUIRE(ldx >= 8 * kLevels + 3, "sdf_head_ws: ldx < 131");
+    Params P{};
+    P.planes = planes, P.chunk_stride = chunk_stride, P.x = x, P.ldx = ldx, P.m = m;
+    P.w_hi = (const __half*)w0s_hi, P.w_lo = (const __half*)w0s_lo, P.w_head = w_head_s, P.b_head = b_head;
+    P.out_scale = out_scale, P.sdf_out = sdf_out;
+    const int64_t tiles = (m + kTileM - 1) / kTileM;
+    const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
+    if (planes) {
+        if (int rc = configure<kSrcPlanes>()) return rc;
+        lattice_sdf_kernel<kSrcPlanes><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);
+    } else {
+        if (int rc = configure<kSrcRows>()) return rc;
+        lattice_sdf_kernel<kSrcRows><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(P);
+    }
+    NA_CHECK_LAUNCH("lattice_sdf_kernel (rows)");
     return NA_OK;
 }

@@ -83,27 +83,44 @@ class PackedSdfMlp:
                     cur.copy_(t)
                 else:
                     setattr(self, name, t.clone())
-        self.epoch = getattr(self, "epoch", 0) + 1
-
-    def lattice_operands(self):
-        """Operands of na_lattice_sdf (packed lazily, once per weight update): (w0s_hi, w0s_lo, w_head_s) with
-        c = beta * log2(e): the split-fp16 image of c * [W0[:, 3:] | W0[:, :3] | b0 | 0 ...] -- the bias rides on a
-        constant-one input column, so the accumulator is the softplus argument in the log2 domain -- and
-        w_head * ln(2) / beta."""
-        if getattr(self, "_lat_epoch", None) != self.epoch:
-            if self.k0 + 1 > self.k0_pad:
-                raise NotImplementedError("no spare input column for the bias")
-            with torch.no_grad():
+            if self.ws_supported():
+                # operands of the warp-specialised SDF-only kernels, packed here (eagerly, in place) so that a captured
+                # graph never contains the packing: c * [W0[:, 3:] | W0[:, :3] | b0 | 0 ...] with c = beta * log2(e) -- the
+                # bias rides on a constant-one input column, the accumulator is the softplus argument in the log2 domain
+                # -- and w_head * ln(2) / beta
                 c = self.beta * math.log2(math.e)
-                w = torch.zeros(self.n, self.k0_pad, dtype=torch.float64, device=self.w0_f32.device)
+                w = torch.zeros(self.n, self.k0_pad, dtype=torch.float64, device=w0.device)
                 w[:, :self.k0 - 3] = self.w0_f32[:, 3:].double() * c
                 w[:, self.k0 - 3:self.k0] = self.w0_f32[:, :3].double() * c
                 w[:, self.k0] = self.b0.double() * c
-                hi, lo = pack_weight(w.float(), self.k0_pad)
-                head = (self.w_head.double() * (math.log(2.0) / self.beta)).float()
-            self._lat = (hi, lo, head)
-            self._lat_epoch = self.epoch
-        return self._lat
+                lat = dict(zip(("w0s_hi", "w0s_lo"), pack_weight(w.float(), self.k0_pad)))
+                lat["w_head_s"] = (self.w_head.double() * (math.log(2.0) / self.beta)).float()
+                for name, t in lat.items():
+                    cur = getattr(self, name, None)
+                    if cur is not None and cur.shape == t.shape and cur.device == t.device:
+                        cur.copy_(t)
+                    else:
+                        setattr(self, name, t)
+
+    def lattice_operands(self):
+        """(w0s_hi, w0s_lo, w_head_s): the pre-scaled operands of na_lattice_sdf / na_sdf_head_ws (see update_)."""
+        if not self.ws_supported():
+            raise NotImplementedError("warp-specialised SDF-only kernels cover base.yaml's network (131 -> 256 -> 1)")
+        return self.w0s_hi, self.w0s_lo, self.w_head_s
+
+    def ws_supported(self):
+        """Shape of the warp-specialised SDF-only kernels (na_lattice_sdf / na_sdf_head_ws): base.yaml's network."""
+        return self.n == 256 and self.k0 == 131 and self.k0_pad == 144
+
+    def _head_ws(self, planes, chunk_stride, rows, m):
+        w_hi, w_lo, head = self.lattice_operands()
+        dev = planes.device if planes is not None else rows.device
+        sdf = torch.empty(m, 1, dtype=torch.float32, device=dev)
+        rc = _L().na_sdf_head_ws(ptr(planes), chunk_stride, ptr(rows), 0 if rows is None else rows.stride(0), m, ptr(w_hi),
+                                 ptr(w_lo), self.k0_pad, self.n, ptr(head), ptr(self.b_head), 1.0, ptr(sdf),
+                                 _lib.current_stream())
+        _lib.check(rc, "na_sdf_head_ws")
+        return sdf
 
     def forward(self, rows, with_sdf=True, with_feat=True, with_hidden=False):
         """rows: [M, K0] fp32 CUDA tensor, unit stride in the last dim (row stride free).
@@ -112,6 +129,8 @@ class PackedSdfMlp:
         assert rows.dim() == 2 and rows.shape[1] == self.k0 and rows.stride(1) == 1 and rows.dtype == torch.float32
         m = rows.shape[0]
         dev = rows.device
+        if with_sdf and not with_feat and not with_hidden and self.ws_supported():
+            return self._head_ws(None, 0, rows, m), None
         sdf = torch.empty(m, 1, dtype=torch.float32, device=dev) if with_sdf else None
         feat = torch.empty(m, self.n, dtype=torch.float32, device=dev) if with_feat else None
         hidden = torch.empty(m, self.n, dtype=torch.float32, device=dev) if with_hidden else None
@@ -132,6 +151,8 @@ class PackedSdfMlp:
         assert planes.dim() == 3 and planes.shape[2] == 8 and planes.stride(2) == 1 and planes.stride(1) == 8
         assert planes.shape[0] * 8 >= self.k0 and planes.shape[1] >= m and planes.dtype == torch.float32
         dev = planes.device
+        if not with_hidden and self.ws_supported() and planes.shape[0] == 17:
+            return self._head_ws(planes, planes.stride(0), None, m)
         sdf = torch.empty(m, 1, dtype=torch.float32, device=dev)
         hidden = torch.empty(m, self.n, dtype=torch.float32, device=dev) if with_hidden else None
         rc = _L().na_sdf_head_fwd_planes(ptr(planes), planes.stride(0), m, self.k0, self.n, ptr(self.w0p_hi),

@@ -73,9 +73,19 @@ def test_pipelined_sdf_only_forward(na_lib, cuda_device, k0, n, m):
     assert (hidden - hidden_2).abs().max().item() <= 1e-7 * max(hidden_2.abs().max().item(), 1.0)   # log1p: polynomial vs lg2
     assert (sdf - sdf_2).abs().max().item() <= 1e-6 * max(ref_sdf.abs().max().item(), 1.0)  # head sum order differs
     assert torch.all(guard == 7.0)
-    # a second launch on the same stream reproduces the first bit for bit
+    # without the hidden activations base.yaml's shape takes the warp-specialised kernel (na_sdf_head_ws: loader warps,
+    # pre-scaled operands, softplus in the log2 domain); other shapes the pipelined kernel again.  A second launch on the
+    # same stream reproduces the first bit for bit, packed and strided rows agree bit for bit.
+    scale = max(ref_sdf.abs().max().item(), 1.0)
     sdf2, _ = packed.forward(xp, with_sdf=True, with_feat=False)
-    assert torch.equal(sdf2, sdf)
+    sdf3, _ = packed.forward(buf[:, 1:], with_sdf=True, with_feat=False)
+    sdf4, _ = packed.forward(xp, with_sdf=True, with_feat=False)
+    assert torch.equal(sdf2, sdf3) and torch.equal(sdf2, sdf4)
+    assert (sdf2.cpu().double() - ref_sdf).abs().max().item() <= 2e-6 * scale
+    if packed.ws_supported():
+        assert (sdf2 - sdf).abs().max().item() <= 1e-6 * scale
+    else:
+        assert torch.equal(sdf2, sdf)
 
 
 @pytest.mark.parametrize("k0,n,m", [(131, 256, 128 * 148 + 300), (131, 256, 77), (67, 128, 1000)])
@@ -101,6 +111,10 @@ def test_sdf_head_from_chunk_planes(na_lib, cuda_device, k0, n, m):
     sdf_r, _, hidden_r = packed.forward(xd.contiguous(), with_sdf=True, with_feat=False, with_hidden=True)
     assert (sdf - sdf_r).abs().max().item() <= 2e-6 * scale
     assert (hidden - hidden_r).abs().max().item() <= 2e-6 * max(hidden_r.abs().max().item(), 1.0)
+    # without the hidden activations: the warp-specialised kernel at base.yaml's shape (na_sdf_head_ws, planes source)
+    sdf_w = packed.forward_planes(planes, m)
+    assert sdf_w.shape == (m, 1) and (sdf_w.cpu().double() - ref_sdf).abs().max().item() <= 2e-6 * scale
+    assert torch.equal(sdf_w, packed.forward_planes(planes, m))
 
 
 def test_finite_difference_gradient_quality(na_lib, cuda_device):
