@@ -377,6 +377,14 @@ typedef struct na_mlp_stage {
 } na_mlp_stage;
 int na_mlp_chain_fwd(const na_mlp_stage* stages, int n_stages, int64_t m, void* stream);
 
+/* One-launch operand packing (csrc/pack.cu): logical W[j, c] = w[j*ld_w + c] (transposed: w[c*ld_w + j]) for j < n_valid,
+ * c < k; rows n_valid..n-1 are zero.  Destination column kd < k takes scale * W[j, (kd + col_rot) mod k], column k takes
+ * scale * extra_col[j] when extra_col is given, the rest up to k_pad is zero.  hi = fp16(v), lo = fp16((v - hi) * 2048),
+ * both in the K-chunk-major layout of the tensor-core kernels: [(k/8)][(j/8)][j%8][k%8].  n multiple of 8, k_pad of 16.
+ * Replaces: the host-side torch packing of the effective weights (weight norm applied) behind mlp.py:55-69. */
+int na_pack_split_f16(const float* w, int64_t ld_w, int n, int n_valid, int k, int transposed, int col_rot, double scale,
+                      const float* extra_col, int k_pad, void* hi, void* lo, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Element-wise glue of the per-ray pipeline, one launch each (csrc/glue.cu).  All tensors fp32 contiguous unless a
  * leading dimension is given; `rows` = rays x samples, `samples_per_ray` maps a row to its ray.

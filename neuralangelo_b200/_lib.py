@@ -73,6 +73,8 @@ def _declare(lib):
                                           vp, vp, ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_float, vp, vp]),
         "na_sdf_head_ws": (ctypes.c_int, [vp, i64, vp, i64, i64, vp, vp, ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_float,
                                           vp, vp]),
+        "na_pack_split_f16": (ctypes.c_int, [vp, i64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                             ctypes.c_double, vp, ctypes.c_int, vp, vp, vp]),
         "na_alpha_weights_fwd": (ctypes.c_int, [vp, i64, ctypes.c_int, vp, vp]),
         "na_alpha_weights_bwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, vp, vp]),
         "na_composite_fwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp]),

@@ -53,54 +53,55 @@ class PackedSdfMlp:
         self.beta = float(beta)
         self.update_(mlp)
 
+    def _pack(self, name, w, n, k, k_pad, n_valid=None, transposed=False, rot=0, scale=1.0, extra=None):
+        """One launch (na_pack_split_f16) into the persistent <name>_hi / <name>_lo tensors: kernels recorded in a CUDA
+        graph keep reading valid, current data from the same addresses."""
+        hi = getattr(self, name + "_hi", None)
+        if hi is None or hi.numel() != n * k_pad or hi.device != w.device:
+            hi = torch.empty(n * k_pad, dtype=torch.float16, device=w.device)
+            setattr(self, name + "_hi", hi)
+            setattr(self, name + "_lo", torch.empty_like(hi))
+        assert w.dtype == torch.float32 and w.stride(1) == 1
+        rc = _L().na_pack_split_f16(ptr(w), w.stride(0), n, n if n_valid is None else n_valid, k, int(transposed), rot,
+                                    float(scale), ptr(extra), k_pad, ptr(hi), ptr(getattr(self, name + "_lo")),
+                                    _lib.current_stream())
+        _lib.check(rc, "na_pack_split_f16")
+
     def update_(self, mlp):
-        """(Re)pack from the module's current weights.  After the first call the packed tensors are updated IN
-        PLACE, so kernels recorded in a CUDA graph keep reading valid, current data from the same addresses."""
+        """(Re)pack from the module's current weights, in place after the first call."""
         l0, l1 = mlp.linears
+        n, k0, k0_pad = self.n, self.k0, self.k0_pad
         with torch.no_grad():
-            new = dict(zip(("w0_hi", "w0_lo"), pack_weight(l0.effective_weight(), self.k0_pad)))
-            new.update(zip(("w1_hi", "w1_lo"), pack_weight(l1.effective_weight(), self.n)))
-            # chunk-plane column order: encoding features first (one 8-wide chunk per level), xyz in the last chunk
-            w0 = l0.effective_weight()
-            new.update(zip(("w0p_hi", "w0p_lo"), pack_weight(torch.cat([w0[:, 3:], w0[:, :3]], dim=1), self.k0_pad)))
-            # operands of the backward products (dz1 W1, dz0 W0): transposed weights in the same packed form, and the
-            # two norms its row scaling uses -- cached here so that a training step packs once, not per call
-            w1 = l1.effective_weight()
-            w0t = torch.zeros(self.k0_pad, self.n, dtype=torch.float32, device=w0.device)
-            w0t[:self.k0] = w0.detach().float().t()
-            new.update(zip(("w0t_hi", "w0t_lo"), pack_weight(w0t, self.n)))
-            new.update(zip(("w1t_hi", "w1t_lo"), pack_weight(w1.detach().float().t().contiguous(), self.n)))
-            new["norms"] = torch.stack([w1.detach().abs().sum(dim=0).max().float(),
-                                        mlp.linear_sdf.weight.detach().abs().max().float()])
-            new["w0_f32"] = w0.detach().float().contiguous()
-            new["b0"] = l0.bias.detach().float().contiguous()
-            new["b1"] = l1.bias.detach().float().contiguous()
-            new["w_head"] = mlp.linear_sdf.weight.detach().float().reshape(-1).contiguous()
-            new["b_head"] = mlp.linear_sdf.bias.detach().float().reshape(1)
+            w0 = l0.effective_weight().detach().float().contiguous()
+            w1 = l1.effective_weight().detach().float().contiguous()
+            new = {"b0": l0.bias.detach().float().contiguous(), "b1": l1.bias.detach().float().contiguous(),
+                   "w_head": mlp.linear_sdf.weight.detach().float().reshape(-1).contiguous(),
+                   "b_head": mlp.linear_sdf.bias.detach().float().reshape(1),
+                   # the two norms the backward's row scaling uses
+                   "norms": torch.stack([w1.abs().sum(dim=0).max(), mlp.linear_sdf.weight.detach().abs().max().float()])}
             for name, t in new.items():
                 cur = getattr(self, name, None)
                 if cur is not None and cur.shape == t.shape and cur.device == t.device:
                     cur.copy_(t)
                 else:
                     setattr(self, name, t.clone())
+            self._pack("w0", w0, n, k0, k0_pad)
+            self._pack("w1", w1, n, n, n)
+            # chunk-plane column order: encoding features first (one 8-wide chunk per level), xyz in the last chunk
+            self._pack("w0p", w0, n, k0, k0_pad, rot=3)
+            # operands of the backward products (dz1 W1, dz0 W0): the transposed weights
+            self._pack("w0t", w0, k0_pad, n, n, n_valid=k0, transposed=True)
+            self._pack("w1t", w1, n, n, n, transposed=True)
             if self.ws_supported():
-                # operands of the warp-specialised SDF-only kernels, packed here (eagerly, in place) so that a captured
-                # graph never contains the packing: c * [W0[:, 3:] | W0[:, :3] | b0 | 0 ...] with c = beta * log2(e) -- the
-                # bias rides on a constant-one input column, the accumulator is the softplus argument in the log2 domain
-                # -- and w_head * ln(2) / beta
-                c = self.beta * math.log2(math.e)
-                w = torch.zeros(self.n, self.k0_pad, dtype=torch.float64, device=w0.device)
-                w[:, :self.k0 - 3] = self.w0_f32[:, 3:].double() * c
-                w[:, self.k0 - 3:self.k0] = self.w0_f32[:, :3].double() * c
-                w[:, self.k0] = self.b0.double() * c
-                lat = dict(zip(("w0s_hi", "w0s_lo"), pack_weight(w.float(), self.k0_pad)))
-                lat["w_head_s"] = (self.w_head.double() * (math.log(2.0) / self.beta)).float()
-                for name, t in lat.items():
-                    cur = getattr(self, name, None)
-                    if cur is not None and cur.shape == t.shape and cur.device == t.device:
-                        cur.copy_(t)
-                    else:
-                        setattr(self, name, t)
+                # operands of the warp-specialised SDF-only kernels: c * [W0[:, 3:] | W0[:, :3] | b0 | 0 ...] with
+                # c = beta * log2(e) -- the bias rides on a constant-one input column, the accumulator is the softplus
+                # argument in the log2 domain -- and w_head * ln(2) / beta
+                self._pack("w0s", w0, n, k0, k0_pad, rot=3, scale=self.beta * math.log2(math.e), extra=self.b0)
+                head = self.w_head * (math.log(2.0) / self.beta)
+                if getattr(self, "w_head_s", None) is not None and self.w_head_s.device == head.device:
+                    self.w_head_s.copy_(head)
+                else:
+                    self.w_head_s = head
 
     def lattice_operands(self):
         """(w0s_hi, w0s_lo, w_head_s): the pre-scaled operands of na_lattice_sdf / na_sdf_head_ws (see update_)."""

@@ -117,6 +117,36 @@ def test_sdf_head_from_chunk_planes(na_lib, cuda_device, k0, n, m):
     assert torch.equal(sdf_w, packed.forward_planes(planes, m))
 
 
+def test_one_launch_operand_packing_matches_the_torch_packing(na_lib, cuda_device):
+    """na_pack_split_f16 (csrc/pack.cu) against fused_mlp.pack_weight (torch ops) bit for bit: plain, column-rotated
+    (chunk-plane order), transposed with zero rows, scaled with the bias as an extra column."""
+    import math
+    from neuralangelo_b200.fused_mlp import PackedSdfMlp, pack_weight
+    mlp = _mlp(131, 256, seed=3).float().to(cuda_device)
+    with torch.no_grad():
+        mlp.linears[0].weight_v[5, 7] = 1e6          # exercises the +-65504 clamp
+    packed = PackedSdfMlp(mlp, beta=100.0)
+    w0 = mlp.linears[0].effective_weight().detach().float()
+    w1 = mlp.linears[1].effective_weight().detach().float()
+
+    def same(name, w, k_pad):
+        hi, lo = pack_weight(w, k_pad)
+        assert torch.equal(getattr(packed, name + "_hi"), hi) and torch.equal(getattr(packed, name + "_lo"), lo), name
+
+    same("w0", w0, 144)
+    same("w1", w1, 256)
+    same("w0p", torch.cat([w0[:, 3:], w0[:, :3]], dim=1), 144)
+    w0t = torch.zeros(144, 256, device=cuda_device)
+    w0t[:131] = w0.t()
+    same("w0t", w0t, 256)
+    same("w1t", w1.t().contiguous(), 256)
+    c = 100.0 * math.log2(math.e)
+    ws = torch.zeros(256, 144, dtype=torch.float64, device=cuda_device)
+    ws[:, :128], ws[:, 128:131], ws[:, 131] = w0[:, 3:].double() * c, w0[:, :3].double() * c, packed.b0.double() * c
+    same("w0s", ws.float(), 144)
+    assert torch.equal(packed.w_head_s, packed.w_head * (math.log(2.0) / 100.0))
+
+
 def test_finite_difference_gradient_quality(na_lib, cuda_device):
     """The reason for the split-precision scheme: central differences at eps = 1/2048 through the fused MLP
     must reproduce the float64 directional derivative (a TF32 single pass is off by O(1) here)."""
