@@ -418,6 +418,16 @@ int na_sdf_losses_fwd(const float* grad, const float* hess, const uint8_t* outsi
 int na_sdf_losses_bwd(const float* grad, const float* hess, const uint8_t* outside, int64_t rows, int samples_per_ray,
                       const float* d_out2, float* d_grad, float* d_hess, void* stream);
 
+/* Ray set-up for the sampled pixels only, one launch: pixel ray_idx[b, r] of the row-major H x W grid (pixel centres at
+ * +0.5) -> center / ray (depth 1) / ray_unit [n_images, rays_per_image, 3] and, when near / far / outside are given, the
+ * unit-sphere bounds with the reference's miss handling (near 1, far 1.2, outside 1).  pose [n_images, 3, 4] world-to-
+ * camera, intr [n_images, 3, 3].
+ * Replaces: camera.get_center_and_ray + slice_by_ray_idx + normalize + get_dist_bounds,
+ * projects/nerf/utils/camera.py:283-311, projects/neuralangelo/model.py:117-121,207-213. */
+int na_ray_setup(const float* pose, const float* intr, const int64_t* ray_idx, int64_t n_images, int rays_per_image,
+                 int width, float* center, float* ray, float* ray_unit, float* near, float* far, uint8_t* outside,
+                 void* stream);
+
 #ifdef __cplusplus
 }
 #endif

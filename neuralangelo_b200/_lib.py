@@ -75,6 +75,7 @@ def _declare(lib):
                                           vp, vp]),
         "na_pack_split_f16": (ctypes.c_int, [vp, i64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                              ctypes.c_double, vp, ctypes.c_int, vp, vp, vp]),
+        "na_ray_setup": (ctypes.c_int, [vp, vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp, vp, vp, vp, vp, vp]),
         "na_alpha_weights_fwd": (ctypes.c_int, [vp, i64, ctypes.c_int, vp, vp]),
         "na_alpha_weights_bwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, vp, vp]),
         "na_composite_fwd": (ctypes.c_int, [vp, vp, i64, ctypes.c_int, ctypes.c_int, vp, vp]),

@@ -61,6 +61,29 @@ def rays_for_indices(pose, intr, image_size, ray_idx):
     return _rays_from_pixels(xy, pose, intr)
 
 
+def ray_setup(pose, intr, image_size, ray_idx, with_bounds=True):
+    """rays_for_indices + normalize + the unit-sphere bounds of Model.get_dist_bounds in ONE launch (na_ray_setup) for
+    CUDA inputs that need no gradient (the reference never differentiates the cameras on this path).  Returns
+    (center, ray, ray_unit [B,R,3], (near, far [B,R,1], outside [B,R,1] bool) | None)."""
+    from . import _lib
+    if not pose.is_cuda:
+        raise _lib.NaError("ray_setup is the CUDA path; use rays_for_indices on the CPU")
+    if torch.is_grad_enabled() and (pose.requires_grad or intr.requires_grad):
+        raise NotImplementedError("ray_setup has no backward: differentiate rays_for_indices instead")
+    H, W = image_size
+    B, R = ray_idx.shape
+    pose_c, intr_c = _lib.f32c(pose.detach()), _lib.f32c(intr.detach())
+    idx = ray_idx.to(torch.int64).contiguous()
+    out = torch.empty(3, B, R, 3, dtype=torch.float32, device=pose.device)
+    bounds = torch.empty(2, B, R, 1, dtype=torch.float32, device=pose.device) if with_bounds else None
+    outside = torch.empty(B, R, 1, dtype=torch.uint8, device=pose.device) if with_bounds else None
+    rc = _lib.lib().na_ray_setup(_lib.ptr(pose_c), _lib.ptr(intr_c), _lib.ptr(idx), B, R, int(W), _lib.ptr(out[0]),
+                                 _lib.ptr(out[1]), _lib.ptr(out[2]), _lib.ptr(bounds[0]) if with_bounds else None,
+                                 _lib.ptr(bounds[1]) if with_bounds else None, _lib.ptr(outside), _lib.current_stream())
+    _lib.check(rc, "na_ray_setup")
+    return out[0], out[1], out[2], ((bounds[0], bounds[1], outside.view(torch.bool)) if with_bounds else None)
+
+
 def get_3D_points_from_dist(center, ray_unit, dist, multi=True):
     """camera.py:314-320: x = c + d * v."""
     if multi:

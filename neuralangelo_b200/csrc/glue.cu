@@ -292,3 +292,90 @@ extern "C" int na_sdf_losses_bwd(const float* grad, const float* hess, const uin
     NA_CHECK_LAUNCH("sdf_losses_bwd_kernel");
     return NA_OK;
 }
+
+// ---- ray set-up for selected pixels: pixel index -> centre, ray, unit ray, unit-sphere bounds --------------------------
+// Follows the reference's order of operations: img2cam with the closed-form inverse intrinsics, cam2world with
+// [R^T | -R^T t] applied to homogeneous coordinates (sum over j = 0..3), ray = world point - centre
+// (projects/nerf/utils/camera.py:283-311), normalize (eps 1e-12), sphere intersection with radius 1 and the miss
+// handling of Model.get_dist_bounds (projects/neuralangelo/model.py:207-213).
+namespace {
+__global__ void ray_setup_kernel(const float* __restrict__ pose, const float* __restrict__ intr,
+                                 const int64_t* __restrict__ ray_idx, int64_t n, int rays_per_image, int width,
+                                 float* __restrict__ center, float* __restrict__ ray, float* __restrict__ ray_unit,
+                                 float* __restrict__ near, float* __restrict__ far, uint8_t* __restrict__ outside) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t b = i / rays_per_image;
+    const float* P = pose + b * 12;
+    const float* K = intr + b * 9;
+    const int64_t idx = ray_idx[i];
+    const float xy1[3] = {(float)(idx % width) + 0.5f, (float)(idx / width) + 0.5f, 1.f};
+    // inverse intrinsics: adjugate / determinant
+    const float a = K[0], bb = K[1], c = K[2], d = K[3], e = K[4], f = K[5], g = K[6], h = K[7], k = K[8];
+    const float A = __fsub_rn(__fmul_rn(e, k), __fmul_rn(f, h)), B = __fsub_rn(__fmul_rn(c, h), __fmul_rn(bb, k)),
+                C = __fsub_rn(__fmul_rn(bb, f), __fmul_rn(c, e));
+    const float D = __fsub_rn(__fmul_rn(f, g), __fmul_rn(d, k)), E = __fsub_rn(__fmul_rn(a, k), __fmul_rn(c, g)),
+                F = __fsub_rn(__fmul_rn(c, d), __fmul_rn(a, f));
+    const float G = __fsub_rn(__fmul_rn(d, h), __fmul_rn(e, g)), H = __fsub_rn(__fmul_rn(bb, g), __fmul_rn(a, h)),
+                I = __fsub_rn(__fmul_rn(a, e), __fmul_rn(bb, d));
+    const float det = __fadd_rn(__fadd_rn(__fmul_rn(a, A), __fmul_rn(bb, D)), __fmul_rn(c, G));
+    const float Ki[3][3] = {{A / det, B / det, C / det}, {D / det, E / det, F / det}, {G / det, H / det, I / det}};
+    float cam[4];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) cam[r] = fmaf(Ki[r][2], xy1[2], fmaf(Ki[r][1], xy1[1], Ki[r][0] * xy1[0]));
+    cam[3] = 1.f;
+    // pose inverse [R^T | -R^T t]
+    float Ri[3][4];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        Ri[r][0] = P[0 * 4 + r], Ri[r][1] = P[1 * 4 + r], Ri[r][2] = P[2 * 4 + r];
+        Ri[r][3] = fmaf(-Ri[r][2], P[2 * 4 + 3], fmaf(-Ri[r][1], P[1 * 4 + 3], -Ri[r][0] * P[0 * 4 + 3]));
+    }
+    float cen[3], dir[3], nrm2 = 0.f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        cen[r] = Ri[r][3];   // [0, 0, 0, 1] . row
+        const float world = fmaf(Ri[r][3], cam[3], fmaf(Ri[r][2], cam[2], fmaf(Ri[r][1], cam[1], Ri[r][0] * cam[0])));
+        dir[r] = world - cen[r];
+        nrm2 = fmaf(dir[r], dir[r], nrm2);
+    }
+    const float den = fmaxf(sqrtf(nrm2), 1e-12f);
+    float u[3], ctc = 0.f, ctv = 0.f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        u[r] = dir[r] / den;
+        ctc = fmaf(cen[r], cen[r], ctc);
+        ctv = fmaf(cen[r], u[r], ctv);
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        center[i * 3 + r] = cen[r];
+        ray[i * 3 + r] = dir[r];
+        ray_unit[i * 3 + r] = u[r];
+    }
+    if (near) {
+        const float disc = sqrtf(ctv * ctv - (ctc - 1.f));   // NaN = the ray misses the unit sphere
+        const float dn = fmaxf(-ctv - disc, 0.f), df = -ctv + disc;
+        const bool miss = disc != disc;
+        near[i] = miss ? 1.f : dn;
+        far[i] = miss ? 1.2f : df;
+        outside[i] = miss ? 1 : 0;
+    }
+}
+}  // namespace
+
+extern "C" int na_ray_setup(const float* pose, const float* intr, const int64_t* ray_idx, int64_t n_images,
+                            int rays_per_image, int width, float* center, float* ray, float* ray_unit, float* near,
+                            float* far, uint8_t* outside, void* stream) {
+    na::clear_error();
+    const int64_t n = n_images * rays_per_image;
+    NA_REQUIRE(n >= 0 && rays_per_image >= 0, "ray_setup: negative sizes");
+    if (n == 0) return NA_OK;
+    NA_REQUIRE(pose && intr && ray_idx && center && ray && ray_unit && width > 0, "ray_setup: bad arguments");
+    NA_REQUIRE((near == nullptr) == (far == nullptr) && (near == nullptr) == (outside == nullptr),
+               "ray_setup: near / far / outside go together");
+    ray_setup_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pose, intr, ray_idx, n, rays_per_image, width,
+                                                                                     center, ray, ray_unit, near, far, outside);
+    NA_CHECK_LAUNCH("ray_setup_kernel");
+    return NA_OK;
+}

@@ -102,9 +102,12 @@ class Model(torch.nn.Module):
         num_rays = self.cfg_render.rand_rays
         all_idx = torch.arange(H * W, device=pose.device).repeat(pose.shape[0], 1)
         for c in range(0, H * W, num_rays):
-            center, ray = camera.rays_for_indices(pose, intr, image_size, all_idx[:, c:c + num_rays])
-            ray_unit = torch_F.normalize(ray, dim=-1)
-            out = self.render_rays(center, ray_unit, sample_idx=sample_idx, stratified=stratified)
+            if pose.is_cuda and not (torch.is_grad_enabled() and (pose.requires_grad or intr.requires_grad)):
+                center, ray, ray_unit, bounds = camera.ray_setup(pose, intr, image_size, all_idx[:, c:c + num_rays])
+            else:
+                center, ray = camera.rays_for_indices(pose, intr, image_size, all_idx[:, c:c + num_rays])
+                ray_unit, bounds = torch_F.normalize(ray, dim=-1), None
+            out = self.render_rays(center, ray_unit, sample_idx=sample_idx, stratified=stratified, bounds=bounds)
             if not self.training:
                 dist = render.composite(out["dists"], out["weights"])
                 out.update(depth=dist / ray.norm(dim=-1, keepdim=True))
@@ -114,14 +117,20 @@ class Model(torch.nn.Module):
         return {key: torch.cat(value, dim=1) for key, value in output.items()}
 
     def render_pixels(self, pose, intr, image_size, stratified=False, sample_idx=None, ray_idx=None):
+        if pose.is_cuda and not (torch.is_grad_enabled() and (pose.requires_grad or intr.requires_grad)):
+            center, _, ray_unit, bounds = camera.ray_setup(pose, intr, image_size, ray_idx)   # one launch
+            return self.render_rays(center, ray_unit, sample_idx=sample_idx, stratified=stratified, bounds=bounds)
         center, ray = camera.rays_for_indices(pose, intr, image_size, ray_idx)
         ray_unit = torch_F.normalize(ray, dim=-1)
         return self.render_rays(center, ray_unit, sample_idx=sample_idx, stratified=stratified)
 
-    def render_rays(self, center, ray_unit, sample_idx=None, stratified=False):
-        """model.py:124-156."""
-        with torch.no_grad():
-            near, far, outside = self.get_dist_bounds(center, ray_unit)
+    def render_rays(self, center, ray_unit, sample_idx=None, stratified=False, bounds=None):
+        """model.py:124-156.  `bounds`: (near, far, outside) when the ray set-up kernel already produced them."""
+        if bounds is not None:
+            near, far, outside = bounds
+        else:
+            with torch.no_grad():
+                near, far, outside = self.get_dist_bounds(center, ray_unit)
         app, app_outside = self.get_appearance_embedding(sample_idx, ray_unit.shape[1])
         obj = self.render_rays_object(center, ray_unit, near, far, outside, app, stratified=stratified)
         bg = self.render_rays_background(center, ray_unit, far, app_outside, stratified=stratified) \

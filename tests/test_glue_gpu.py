@@ -119,3 +119,43 @@ def test_sdf_losses_match_reference_expression(na_lib, cuda_device, with_hess, w
     if with_hess:
         fin_h = torch.isfinite(hd.grad).all(dim=-1)
         _close(hk.grad.cpu()[fin_h], hd.grad[fin_h], 2e-6, "d_hessians")
+
+
+def test_ray_setup_matches_the_reference_formulation(na_lib, cuda_device):
+    """na_ray_setup (pixel index -> centre, ray, unit ray, unit-sphere bounds; one launch) against the torch formulation of
+    camera.py:283-311 + model.py:117-121,207-213 evaluated in float64, for cameras whose rays hit and miss the sphere."""
+    from neuralangelo_b200 import camera, nerf_util
+    g = torch.Generator().manual_seed(3)
+    B, R, H, W = 3, 4096, 600, 800
+    poses = []
+    for b in range(B):
+        eye = torch.randn(3, generator=g, dtype=torch.float64)
+        eye = eye / eye.norm() * (2.0 + b)
+        fwd = -eye / eye.norm()
+        right = torch.linalg.cross(torch.tensor([0.0, 1.0, 0.0], dtype=torch.float64), fwd)
+        right = right / right.norm()
+        Rm = torch.stack([right, torch.linalg.cross(fwd, right), fwd])
+        poses.append(torch.cat([Rm, (-Rm @ eye)[:, None]], dim=1))
+    pose = torch.stack(poses)
+    intr = torch.tensor([[700.0, 0.3, 400.0], [0.0, 710.0, 300.0], [0.0, 0.0, 1.0]], dtype=torch.float64).repeat(B, 1, 1)
+    idx = torch.randint(0, H * W, (B, R), generator=g)
+    xy = torch.stack([(idx % W).double() + 0.5, torch.div(idx, W, rounding_mode="floor").double() + 0.5], dim=-1)
+    center64, ray64 = camera._rays_from_pixels(xy, pose, intr)
+    unit64 = torch.nn.functional.normalize(ray64, dim=-1)
+    near64, far64 = nerf_util.intersect_with_sphere(center64, unit64, radius=1.0)
+    c, r, u, (near, far, outside) = camera.ray_setup(pose.float().to(cuda_device), intr.float().to(cuda_device), (H, W),
+                                                     idx.to(cuda_device))
+    assert c.shape == (B, R, 3) and near.shape == (B, R, 1) and outside.dtype == torch.bool
+    assert (c.cpu().double() - center64).abs().max().item() <= 2e-6 * center64.abs().max().item()
+    assert (r.cpu().double() - ray64).abs().max().item() <= 5e-6 * ray64.abs().max().item()   # world point minus centre
+    assert (u.cpu().double() - unit64).abs().max().item() <= 5e-6
+    disc2 = ((center64 * unit64).sum(-1, keepdim=True) ** 2 - ((center64 * center64).sum(-1, keepdim=True) - 1.0))
+    hit, miss = disc2 > 1e-3, disc2 < -1e-3
+    assert hit.any() and miss.any()
+    assert bool((outside.cpu() == near64.isnan())[hit | miss].all())
+    assert (near.cpu().double() - near64.clamp_min(0.0))[hit].abs().max().item() <= 2e-4
+    assert (far.cpu().double() - far64)[hit].abs().max().item() <= 2e-4
+    assert bool((near.cpu()[miss] == 1.0).all()) and bool((far.cpu()[miss] == torch.tensor(1.2).float()).all())
+    # no backward: differentiable cameras must take the torch formulation
+    with pytest.raises(NotImplementedError):
+        camera.ray_setup(pose.float().to(cuda_device).requires_grad_(), intr.float().to(cuda_device), (H, W), idx.to(cuda_device))
