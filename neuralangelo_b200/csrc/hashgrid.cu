@@ -52,16 +52,17 @@ __device__ __forceinline__ Level load_level(const na_hashgrid_desc& d, uint32_t 
     return L;
 }
 
+// The modulo proper lives out of line: a 32-bit division is ~25 instructions, entry_index() is inlined once per table
+// row of the unrolled kernels (104 times in the 7-tap backward), and it is taken only by non-power-of-two levels at the
+// wrap-around of the far faces.  Inline, those divisions were most of the kernels' code (the backward's 6 320
+// instructions = 100 KB of SASS streamed through the instruction caches by every warp).
+__device__ __noinline__ uint32_t wrap_index(uint32_t idx, uint32_t entries) { return idx % entries; }
+
 // tcnn grid_index(): dense stride walk or the coherent prime hash, then modulo the level size.
 __device__ __forceinline__ uint32_t entry_index(const Level& L, uint32_t cx, uint32_t cy, uint32_t cz) {
-    uint32_t idx;
-    if (L.hashed) {
-        idx = cx ^ (cy * 2654435761u) ^ (cz * 805459861u);
-        idx = L.pow2mask ? (idx & L.pow2mask) : (idx % L.entries);
-    } else {
-        idx = cx + cy * L.res + cz * L.res * L.res;
-        if (idx >= L.entries) idx %= L.entries;  // only the documented wrap-around at the far faces
-    }
+    uint32_t idx = L.hashed ? (cx ^ (cy * 2654435761u) ^ (cz * 805459861u)) : (cx + cy * L.res + cz * L.res * L.res);
+    if (L.pow2mask) idx &= L.pow2mask;
+    else if (idx >= L.entries) idx = wrap_index(idx, L.entries);
     return idx;
 }
 
@@ -434,6 +435,13 @@ __device__ __forceinline__ F8 f8_load_keep(const float* p, uint64_t pol) { retur
 __device__ __forceinline__ F8 f8_load_stream(const float* p, uint64_t pol) { return na::ldg_f4_stream_hint(p, pol); }
 __device__ __forceinline__ void f8_store_stream(float* p, const F8& v, uint64_t pol) { na::st_f4_hint(p, v, pol); }
 __device__ __forceinline__ void f8_red(float* p, const F8& v, uint64_t pol) { na::red_add_f4_hint(p, v, pol); }
+// predicated in PTX (no branch: the eight corner reductions of a point stay one straight-line sequence)
+__device__ __forceinline__ void f8_red_if(float* p, const F8& v, uint64_t pol, bool on) {
+    asm volatile(
+        "{\n.reg .pred q;\nsetp.ne.b32 q, %6, 0;\n@q red.relaxed.gpu.global.add.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;\n}" ::"l"(p),
+        "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol), "r"((uint32_t)on)
+        : "memory");
+}
 
 struct AxisCell {
     uint32_t c[3];   // cell of tap 0
@@ -655,12 +663,14 @@ hashgrid_axis_fwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
     }
 }
 
-template <int NT>
+// SPLIT: only rows in [row_lo, row_hi) of the level receive their reductions (the caller covers the level in two passes, so
+// that the half being written -- 64 MiB of a 2^22-entry level -- stays in the L2 while 2^22 random points scatter into it).
+template <int NT, bool SPLIT>
 __global__ void __launch_bounds__(kThreads, 3)
 hashgrid_axis_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ x, int64_t n_points,
                          na_unit_map map, const AxisTaps taps, const float* __restrict__ dout, int64_t dout_stride,
                          int64_t dout_tap_stride, int64_t dout_level_stride, float* __restrict__ dtable,
-                         uint32_t level_base) {
+                         uint32_t level_base, uint32_t row_lo, uint32_t row_hi) {
     constexpr int F = 8;
     __shared__ LevelS sl[NA_MAX_LEVELS];
     stage_levels(desc, sl);
@@ -688,14 +698,22 @@ hashgrid_axis_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
     for (int a = 1; a < 3; ++a) S[a][0] = f8_zero(), S[a][1] = f8_zero();
     if (NT > 1) {
         // four rows of the face at cell coordinate `ca` along axis A receive e, weighted by the other two axes
+        auto red_row = [&](uint32_t idx, const F8& v) {
+            if (SPLIT) f8_red_if(tb + (size_t)idx * F, v, keep, idx >= row_lo && idx < row_hi);
+            else f8_red(tb + (size_t)idx * F, v, keep);
+        };
+        // four rows of the face at cell coordinate `ca` along axis A receive e, weighted by the other two axes
         auto face = [&](auto axis_tag, uint32_t ca, const F8& e) {
             constexpr int A = decltype(axis_tag)::value, B = (A + 1) % 3, Cc = (A + 2) % 3;
 #pragma unroll
             for (int sc = 0; sc < 2; ++sc)
 #pragma unroll
                 for (int sb = 0; sb < 2; ++sb)
-                    f8_red(tb + (size_t)axis_row<A>(L, C, ca, sb, sc) * F, f8_scale(C.W[B][sb] * C.W[Cc][sc], e), keep);
+                    red_row(axis_row<A>(L, C, ca, sb, sc), f8_scale(C.W[B][sb] * C.W[Cc][sc], e));
         };
+        // a tap adds (1 - w) g to the face at its cell and w g to the next one; a face that belongs to tap 0's cell is
+        // booked on that cell's slot sum, any other one is scattered on its own (ONE face() site per half: the kernel's
+        // code size is what the instruction caches see)
         auto axis_taps = [&](auto axis_tag) {
             constexpr int A = decltype(axis_tag)::value;
 #pragma unroll
@@ -706,18 +724,13 @@ hashgrid_axis_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
                 uint32_t cell;
                 axis_tap(L, map, xs[A], taps.d[t - 1], C.ci[A], delta, w, cell);
                 const F8& gt = gv[t < NT ? t : 0];
-                if (delta == 0) {
-                    f8_axpy(S[A][0], 1.f - w, gt);
-                    f8_axpy(S[A][1], w, gt);
-                } else if (delta == 1) {
-                    f8_axpy(S[A][1], 1.f - w, gt);
-                    face(axis_tag, cell + 1u, f8_scale(w, gt));
-                } else if (delta == -1) {
-                    f8_axpy(S[A][0], w, gt);
-                    face(axis_tag, cell, f8_scale(1.f - w, gt));
-                } else {
-                    face(axis_tag, cell, f8_scale(1.f - w, gt));
-                    face(axis_tag, cell + 1u, f8_scale(w, gt));
+#pragma unroll
+                for (int hf = 0; hf < 2; ++hf) {
+                    const int rel = delta + hf;
+                    const float wh = hf ? w : 1.f - w;
+                    if (rel == 0) f8_axpy(S[A][0], wh, gt);
+                    else if (rel == 1) f8_axpy(S[A][1], wh, gt);
+                    else face(axis_tag, cell + (uint32_t)hf, f8_scale(wh, gt));
                 }
             }
         };
@@ -737,7 +750,8 @@ hashgrid_axis_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
                     f8_axpy(v, C.W[0][kx] * C.W[1][ky], S[2][kz]);
                 }
                 const uint32_t idx = entry_index(L, C.c[0] + kx, C.c[1] + ky, C.c[2] + kz);
-                f8_red(tb + (size_t)idx * F, v, keep);
+                if (SPLIT) f8_red_if(tb + (size_t)idx * F, v, keep, idx >= row_lo && idx < row_hi);
+                else f8_red(tb + (size_t)idx * F, v, keep);
             }
     }
 }
@@ -890,13 +904,38 @@ int launch_bwd(const na_hashgrid_desc* desc, const float* x, int64_t n_points, n
             !dev_knobs().generic) {
             const int64_t nb = (n_points + kAxisPoints - 1) / kAxisPoints;
             NA_REQUIRE(nb <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
-            dim3 g((unsigned)nb, active_levels - level_base);
-if (tp.n == 1)
-                hashgrid_axis_bwd_kernel<1><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
-                                                                        dout_tap_stride, dout_level_stride, dtable, level_base);
-            else
-                hashgrid_axis_bwd_kernel<7><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
-                                                                        dout_tap_stride, dout_level_stride, dtable, level_base);
+            // Large batches: the finest levels (most cell-crossing taps, 128 MiB of gradient each) are covered in two passes
+            // over disjoint halves of their rows; measured on 2^22 points x 7 taps: 8.10 -> 7.83 ms with the last two
+            // levels split, no gain from splitting more (profiles/r02_hashgrid.md).
+            uint32_t split = active_levels;
+            if (n_points >= (1 << 21) && tp.n == 7)
+                while (split > level_base && split + 2 > active_levels && desc->hashed[split - 1] &&
+                       (uint64_t)desc->entries[split - 1] * F * 4 > (96ull << 20))
+                    --split;
+#ifdef NA_HG_DEV_KNOBS
+            if (const char* es = getenv("NA_HG_SPLIT")) split = (uint32_t)atoi(es);
+            if (split < level_base) split = level_base;
+            if (split > active_levels) split = active_levels;
+#endif
+            auto launch = [&](uint32_t l0, uint32_t l1, bool part, uint32_t lo, uint32_t hi) {
+                if (l1 <= l0) return;
+                dim3 g((unsigned)nb, l1 - l0);
+                if (tp.n == 1)
+                    hashgrid_axis_bwd_kernel<1, false><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
+                                                                                   dout_tap_stride, dout_level_stride, dtable, l0, lo, hi);
+                else if (!part)
+                    hashgrid_axis_bwd_kernel<7, false><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
+                                                                                   dout_tap_stride, dout_level_stride, dtable, l0, lo, hi);
+                else
+                    hashgrid_axis_bwd_kernel<7, true><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
+                                                                                  dout_tap_stride, dout_level_stride, dtable, l0, lo, hi);
+            };
+            launch(level_base, split, false, 0u, 0xffffffffu);
+            for (uint32_t l = split; l < active_levels; ++l) {
+                const uint32_t half = (desc->entries[l] + 1) / 2;
+                launch(l, l + 1, true, 0u, half);
+                launch(l, l + 1, true, half, 0xffffffffu);
+            }
             NA_CHECK_LAUNCH("hashgrid_axis_bwd_kernel");
             return NA_OK;
         }
