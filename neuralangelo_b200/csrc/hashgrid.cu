@@ -665,8 +665,11 @@ hashgrid_axis_fwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const fl
 
 // SPLIT: only rows in [row_lo, row_hi) of the level receive their reductions (the caller covers the level in two passes, so
 // that the half being written -- 64 MiB of a 2^22-entry level -- stays in the L2 while 2^22 random points scatter into it).
+#ifndef NA_HG_BWD_CTAS
+#define NA_HG_BWD_CTAS 3
+#endif
 template <int NT, bool SPLIT>
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(kThreads, NA_HG_BWD_CTAS)
 hashgrid_axis_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ x, int64_t n_points,
                          na_unit_map map, const AxisTaps taps, const float* __restrict__ dout, int64_t dout_stride,
                          int64_t dout_tap_stride, int64_t dout_level_stride, float* __restrict__ dtable,
@@ -905,11 +908,11 @@ int launch_bwd(const na_hashgrid_desc* desc, const float* x, int64_t n_points, n
             const int64_t nb = (n_points + kAxisPoints - 1) / kAxisPoints;
             NA_REQUIRE(nb <= 0x7fffffffLL, "hashgrid: n_points too large for one launch");
             // Large batches: the finest levels (most cell-crossing taps, 128 MiB of gradient each) are covered in two passes
-            // over disjoint halves of their rows; measured on 2^22 points x 7 taps: 8.10 -> 7.83 ms with the last two
-            // levels split, no gain from splitting more (profiles/r02_hashgrid.md).
+            // over disjoint halves of their rows; measured on 2^22 points x 7 taps: 7.73 ms unsplit, 7.39 / 7.29 / 7.33 ms
+            // with the last 2 / 4 / 6 levels split (profiles/r02_hashgrid.md).
             uint32_t split = active_levels;
             if (n_points >= (1 << 21) && tp.n == 7)
-                while (split > level_base && split + 2 > active_levels && desc->hashed[split - 1] &&
+                while (split > level_base && split + 4 > active_levels && desc->hashed[split - 1] &&
                        (uint64_t)desc->entries[split - 1] * F * 4 > (96ull << 20))
                     --split;
 #ifdef NA_HG_DEV_KNOBS
