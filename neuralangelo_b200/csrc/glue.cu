@@ -83,6 +83,9 @@ rgb_input_fwd_kernel(const float* __restrict__ points, const float* __restrict__
         const float* a = app + row * ld_app;
         for (int i = lane; i < n_app; i += 32) of[n_feat + i] = a[i];
     }
+    // columns up to the leading dimension are zero: the caller may hand the padded rows to a GEMM whose K must be a
+    // multiple of four for the library's vectorised kernels (278 -> 280)
+    for (int64_t i = 6 + n_sh + n_feat + n_app + lane; i < ld_out; i += 32) o[i] = 0.f;
 }
 
 // d_grad from the normal columns of d_out: n = g / r  =>  dg = (dn - n (n . dn)) / r   (r = max(|g|, 1e-12)).

@@ -16,7 +16,7 @@ _L = _lib.lib
 
 class _RgbInput(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, points, ray_unit, grad, feat, app, samples_per_ray, sh_levels):
+    def forward(ctx, points, ray_unit, grad, feat, app, samples_per_ray, sh_levels, pad_to=1):
         _lib.require_cuda(points, ray_unit, grad, feat)
         points, ray_unit, grad = f32c(points), f32c(ray_unit), f32c(grad)
         feat = feat if (feat.dtype == torch.float32 and feat.stride(-1) == 1) else f32c(feat)
@@ -26,10 +26,11 @@ class _RgbInput(torch.autograd.Function):
             app = f32c(app)
         n_sh = (sh_levels + 1) ** 2
         width = 6 + n_sh + n_feat + n_app
-        out = torch.empty(rows, width, dtype=torch.float32, device=feat.device)
+        ld = (width + pad_to - 1) // pad_to * pad_to       # the kernel zero-fills columns width .. ld-1
+        out = torch.empty(rows, ld, dtype=torch.float32, device=feat.device)
         _lib.check(_L().na_rgb_input_fwd(ptr(points), ptr(ray_unit), ptr(grad), ptr(feat), feat.stride(0), ptr(app),
                                          0 if app is None else app.stride(0), rows, int(samples_per_ray), int(sh_levels),
-                                         n_feat, n_app, ptr(out), width, _lib.current_stream()), "na_rgb_input_fwd")
+                                         n_feat, n_app, ptr(out), ld, _lib.current_stream()), "na_rgb_input_fwd")
         ctx.save_for_backward(grad)
         ctx.cols = (3 + n_sh, 6 + n_sh, n_feat, n_app)
         return out
@@ -47,17 +48,18 @@ class _RgbInput(torch.autograd.Function):
                                              _lib.current_stream()), "na_rgb_input_bwd")
         d_feat = d_out[:, feat_col:feat_col + n_feat] if ctx.needs_input_grad[3] else None       # a view: no copy
         d_app = d_out[:, feat_col + n_feat:feat_col + n_feat + n_app] if (n_app and ctx.needs_input_grad[4]) else None
-        return None, None, d_grad, d_feat, d_app, None, None
+        return None, None, d_grad, d_feat, d_app, None, None, None
 
 
-def rgb_input(points, ray_unit, gradients, feats, app, sh_levels):
+def rgb_input(points, ray_unit, gradients, feats, app, sh_levels, pad_to=1):
     """points / gradients [B,R,N,3], ray_unit [B,R,3], feats [B,R,N,F], app [B,R,N,A] | None ->
-    [B,R,N, 3 + (sh_levels+1)^2 + 3 + F + A]: cat([points, SH(ray_unit), normalize(gradients), feats, app])."""
+    [B,R,N, 3 + (sh_levels+1)^2 + 3 + F + A]: cat([points, SH(ray_unit), normalize(gradients), feats, app]), with zero
+    columns appended up to a multiple of `pad_to` (mlp.linear pads the first layer's weight to match)."""
     lead = feats.shape[:-1]
     n = feats.shape[-2]
     out = _RgbInput.apply(points.reshape(-1, 3), ray_unit.reshape(-1, 3), gradients.reshape(-1, 3),
                           feats.reshape(-1, feats.shape[-1]), None if app is None else app.reshape(-1, app.shape[-1]),
-                          n, sh_levels)
+                          n, sh_levels, pad_to)
     return out.view(*lead, out.shape[-1])
 
 

@@ -98,7 +98,12 @@ class _LinearTallRows(torch.autograd.Function):
 
 
 def linear(x, w, b):
-    """F.linear; on CUDA with many rows and a graph to build, the variant whose weight gradient is split-K."""
+    """F.linear; on CUDA with many rows and a graph to build, the variant whose weight gradient is split-K.  `x` may carry
+    ZERO columns beyond the layer's input width (glue.rgb_input pads 278 -> 280 so that K is a multiple of four and the
+    library picks its vectorised GEMMs: 30 us instead of 112 us forward, 36 instead of 126 us for dx at 65 536 rows): the
+    weight is zero-padded to match, autograd slices its gradient back."""
+    if x.shape[-1] > w.shape[-1]:
+        w = F.pad(w, (0, x.shape[-1] - w.shape[-1]))
     if x.is_cuda and x.dim() == 2 and x.shape[0] >= 1024 and b is not None and torch.is_grad_enabled() and \
             (w.requires_grad or x.requires_grad):
         return _LinearTallRows.apply(x, w, b)

@@ -412,7 +412,9 @@ class NeuralRGB(torch.nn.Module):
         if input_vec.is_cuda and _chain_supported(self.mlp):
             # tcgen05 chain kernel (csrc/mlp_chain.cu): all five layers + sigmoid in one launch
             from . import fused_chain
-            flat = input_vec.reshape(-1, input_vec.shape[-1]).float().contiguous()
+            k_in = self.mlp.linears[0].weight_shape()[1] if hasattr(self.mlp.linears[0], "weight_shape") else \
+                self.mlp.linears[0].in_features
+            flat = input_vec.reshape(-1, input_vec.shape[-1])[:, :k_in].float().contiguous()   # without any zero padding
             needs_graph = torch.is_grad_enabled() and (flat.requires_grad or any(p.requires_grad for p in self.mlp.parameters()))
             if not needs_graph:
                 out = fused_chain.mlp_forward(self.mlp, flat, final_act="sigmoid")
@@ -437,7 +439,10 @@ class NeuralRGB(torch.nn.Module):
         if self.cfg_rgb.mode == "idr" and self.cfg_rgb.encoding_view.type == "spherical" and feats.is_cuda and \
                 self.cfg_rgb.encoding_view.levels <= 4:
             from . import glue
-            input_vec = glue.rgb_input(points_3D, ray_unit, gradients, feats, app, self.cfg_rgb.encoding_view.levels)
+            # with a graph to build the rows go to library GEMMs: K padded to a multiple of four (see mlp.linear)
+            pad = 4 if (torch.is_grad_enabled() and not FUSED_CHAIN_IN_TRAINING and not self.mlp.skip_connection) else 1
+            input_vec = glue.rgb_input(points_3D, ray_unit, gradients, feats, app, self.cfg_rgb.encoding_view.levels,
+                                       pad_to=pad)
             return self._run_mlp(input_vec)
         normals = F.normalize(gradients, dim=-1)
         rays_unit = ray_unit[..., None, :].expand_as(points_3D).contiguous()
