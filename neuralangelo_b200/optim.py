@@ -100,18 +100,25 @@ class FusedAdamW:
         n_active, _ = self.active_prefix()
         return self.flat_g, self.table.grad[:n_active]
 
-    def step(self, grad_scale=1.0, lr=None):
-        """One optimizer step on this rank's (already reduced) gradients."""
+    def step(self, grad_scale=1.0, lr=None, after_small=None):
+        """One optimizer step on this rank's (already reduced) gradients.  `after_small`: a callable that needs the small
+        bucket's new values only (operand re-packing); with it the small bucket runs on a side stream beside the table's
+        update, and the caller calls wait_pending() before it touches parameters or gradients again."""
         lr = self.lr if lr is None else lr
         self.step_count += 1
         b1, b2 = self.betas
         stream = _lib.current_stream()
-        _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
-                                      self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
-                                      grad_scale, 1, stream), "na_adamw_step")
-        sdf_mod = getattr(self.model, "neural_sdf", None)
-        if sdf_mod is not None and hasattr(sdf_mod, "invalidate_packed_weights"):
-            sdf_mod.invalidate_packed_weights()   # the kernel above rewrote the MLP weights behind torch's back
+        if after_small is not None and self.table is not None and self.flat_p.is_cuda:
+            self._small_bucket_async(None, lr, grad_scale, after_small)
+        else:
+            _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
+                                          self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
+                                          grad_scale, 1, stream), "na_adamw_step")
+            sdf_mod = getattr(self.model, "neural_sdf", None)
+            if sdf_mod is not None and hasattr(sdf_mod, "invalidate_packed_weights"):
+                sdf_mod.invalidate_packed_weights()   # the kernel above rewrote the MLP weights behind torch's back
+            if after_small is not None:
+                after_small()
         if self.table is None:
             return
         n_active, active = self.active_prefix()
@@ -215,7 +222,7 @@ class FusedAdamW:
         dist.barrier(group=group)
         return True
 
-    def step_multimem(self, rank, world, lr=None):
+    def step_multimem(self, rank, world, lr=None, after_small=None):
         """Same update as step_sharded; the table's exchange and update are ONE kernel over NVLink multicast."""
         import torch.distributed as dist
         import ctypes
@@ -226,6 +233,9 @@ class FusedAdamW:
         stream = _lib.current_stream()
         scale = 1.0 / world
         small = dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, async_op=True)
+        if after_small is not None:           # small bucket + re-packing beside the multicast kernel
+            self._small_bucket_async(small, lr, scale, after_small)
+            small = None
         n_active, active = self.active_prefix()
         p = self.table
         assert n_active % (4 * world) == 0, "active prefix must split evenly across ranks"
@@ -249,14 +259,23 @@ class FusedAdamW:
                                                self.eps, self.weight_decay, self.step_count, scale, 0, 0, stream),
                    "na_adamw_step_multimem")
         mc["p"].barrier(channel=1)            # every rank's slice has landed everywhere, every gradient has been read
-        self.table.grad[:n_active].zero_()
-        small.wait()
-        _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
-                                      self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
-                                      scale, 1, stream), "na_adamw_step")
-        sdf_mod = getattr(self.model, "neural_sdf", None)
-        if sdf_mod is not None and hasattr(sdf_mod, "invalidate_packed_weights"):
-            sdf_mod.invalidate_packed_weights()
+        # the local gradient clear (1.46 GB, 0.2 ms) runs on a side stream; wait_pending() joins it before the next
+        # backward can touch the gradient
+        cur = torch.cuda.current_stream()
+        if getattr(self, "_zero_stream", None) is None:
+            self._zero_stream = torch.cuda.Stream(device=self.table.device)
+        self._zero_stream.wait_stream(cur)
+        with torch.cuda.stream(self._zero_stream):
+            self.table.grad[:n_active].zero_()
+        self._zero_pending = True
+        if small is not None:
+            small.wait()
+            _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
+                                          self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
+                                          scale, 1, stream), "na_adamw_step")
+            sdf_mod = getattr(self.model, "neural_sdf", None)
+            if sdf_mod is not None and hasattr(sdf_mod, "invalidate_packed_weights"):
+                sdf_mod.invalidate_packed_weights()
         if self.lazy and self.applied_levels < self.n_levels:
             self.pending_log_decay += math.log1p(-lr * self.weight_decay)
 
@@ -280,8 +299,41 @@ class FusedAdamW:
                                              math.exp(self.pending_log_decay), _lib.current_stream()), "na_scale_inplace")
         self.pending_log_decay = 0.0
 
+    def _small_bucket_async(self, wait_handle, lr, scale, after_small):
+        """AdamW on the small bucket -- and `after_small()`, the operand re-packing that depends on it -- on a side stream,
+        beside the table's update on the current stream (1.95 ms of HBM streaming on one GPU, 3.2 ms of NVLink traffic on
+        eight).  wait_pending() joins it before the next forward reads the parameters."""
+        cur = torch.cuda.current_stream()
+        if getattr(self, "_small_stream", None) is None:
+            self._small_stream = torch.cuda.Stream(device=self.flat_p.device)
+        side = self._small_stream
+        side.wait_stream(cur)
+        b1, b2 = self.betas
+        with torch.cuda.stream(side):
+            if wait_handle is not None:
+                wait_handle.wait()
+            _lib.check(_L().na_adamw_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v),
+                                          self.flat_p.numel(), lr, b1, b2, self.eps, self.weight_decay, self.step_count,
+                                          scale, 1, _lib.current_stream()), "na_adamw_step")
+            sdf_mod = getattr(self.model, "neural_sdf", None)
+            if sdf_mod is not None and hasattr(sdf_mod, "invalidate_packed_weights"):
+                sdf_mod.invalidate_packed_weights()   # the kernel above rewrote the MLP weights behind torch's back
+            if after_small is not None:
+                after_small()
+        self._small_pending = True
+
+    def wait_pending(self):
+        """Make the current stream wait for the side-stream work of the last step (gradient clear, small bucket)."""
+        if getattr(self, "_zero_pending", False):
+            torch.cuda.current_stream().wait_stream(self._zero_stream)
+            self._zero_pending = False
+        if getattr(self, "_small_pending", False):
+            torch.cuda.current_stream().wait_stream(self._small_stream)
+            self._small_pending = False
+
     def zero_grad(self):
         """Gradients are cleared by step(); this is for the case no step was taken."""
+        self.wait_pending()
         self.flat_g.zero_()
         if self.table is not None:
             n_active, _ = self.active_prefix()

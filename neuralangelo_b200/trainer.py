@@ -168,6 +168,7 @@ class TrainStep:
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
             self.phase_events.append(ev)
             ev[0].record()
+        self.optim.wait_pending()
         if self.use_cuda_graph:
             loss = self._graphed_forward_backward(data)
         else:
@@ -176,23 +177,29 @@ class TrainStep:
             ev[1].record()
         lr = self.base_lr * self.lr_factor(it)
         world = parallel.world_size() if self.data_parallel else 1
+        def repack():
+            # outside any captured graph (see NeuralSDF); the colour / background operands of the chain kernel are
+            # re-packed in place when training uses it, else lazily at their next graph-free use
+            self.model.neural_sdf.refresh_packed_weights()
+            from . import modules
+            if modules.FUSED_CHAIN_IN_TRAINING:
+                fused_chain.refresh_packs()
+            else:
+                fused_chain.invalidate_packs()
+
         if world > 1 and self.optim.table is not None and self.optim.lazy:
             import torch.distributed as dist
-            if self.multimem:
-                self.optim.step_multimem(dist.get_rank(), world, lr=lr)    # one kernel over NVLink multicast
-            else:
-                self.optim.step_sharded(dist.get_rank(), world, lr=lr)     # reduce-scatter / owner update / all-gather
+            if self.multimem:      # one kernel over NVLink multicast; small bucket + re-packing beside it
+                self.optim.step_multimem(dist.get_rank(), world, lr=lr, after_small=repack)
+            else:                  # reduce-scatter / owner update / all-gather
+                self.optim.step_sharded(dist.get_rank(), world, lr=lr)
+                repack()
         elif world == 1:
-            self.optim.step(grad_scale=1.0, lr=lr)
+            self.optim.step(grad_scale=1.0, lr=lr, after_small=repack)
         else:
             grad_scale = parallel.allreduce_gradients(*self.optim.grad_views())
-            self.optim.step(grad_scale=grad_scale, lr=lr)
-        self.model.neural_sdf.refresh_packed_weights()   # outside any captured graph (see NeuralSDF)
-        from . import modules
-        if modules.FUSED_CHAIN_IN_TRAINING:
-            fused_chain.refresh_packs()      # colour / background operands re-packed in place, outside the captured graph
-        else:
-            fused_chain.invalidate_packs()   # only graph-free evaluations use them: re-pack lazily at the next use
+            self.optim.step(grad_scale=grad_scale, lr=lr, after_small=repack)
+        self.optim.wait_pending()      # stream-level join of the side streams: whatever follows sees the whole update
         if ev:
             ev[2].record()
         self.current_iteration += 1
