@@ -323,8 +323,9 @@ def run_ours(args, rank, local_rank, world):
                      "kernel_ms": dominant[2], "algorithmic_bytes": dominant[1],
                      "launches_per_call": {"hashgrid_axis_fwd_kernel": 1, "hashgrid_axis_bwd_kernel": bwd_launches},
                      "note": "kernel_ms / achieved / traffic are per backward (forward) CALL: the backward is "
-                             f"{bwd_launches} launches of the same kernel (coarse levels in one, each of the finest hashed "
-                             "levels in two row-range passes), timed and profiled as one unit",
+                             f"{bwd_launches} launches of the same kernel (dense levels interleaved in one, the other coarse "
+                             "levels in one, each of the finest hashed levels in two row-range passes), timed and profiled "
+                             "as one unit",
                      "other_kernels": {"hashgrid_axis_fwd_kernel": {"ms": fwd_ms, "GBps": fwd_bytes / fwd_ms / 1e6},
                                        "hashgrid_axis_bwd_kernel": {"ms": bwd_ms, "GBps": bwd_bytes / bwd_ms / 1e6}}},
     }

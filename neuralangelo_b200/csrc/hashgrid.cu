@@ -673,16 +673,19 @@ __global__ void __launch_bounds__(kThreads, NA_HG_BWD_CTAS)
 hashgrid_axis_bwd_kernel(const __grid_constant__ na_hashgrid_desc desc, const float* __restrict__ x, int64_t n_points,
                          na_unit_map map, const AxisTaps taps, const float* __restrict__ dout, int64_t dout_stride,
                          int64_t dout_tap_stride, int64_t dout_level_stride, float* __restrict__ dtable,
-                         uint32_t level_base, uint32_t row_lo, uint32_t row_hi) {
+                         uint32_t level_base, uint32_t row_lo, uint32_t row_hi, uint32_t interleave) {
     constexpr int F = 8;
     __shared__ LevelS sl[NA_MAX_LEVELS];
     stage_levels(desc, sl);
     const int sub = threadIdx.x & 1;
-    const uint32_t level = level_base + blockIdx.y;
+    // interleave > 0: consecutive CTAs work on `interleave` different levels (the small dense levels, whose few rows are
+    // hammered by every point: spreading the resident CTAs over several levels spreads the L2's same-address reductions)
+    const uint32_t level = level_base + (interleave ? blockIdx.x % interleave : blockIdx.y);
+    const uint32_t point_block = interleave ? blockIdx.x / interleave : blockIdx.x;
     const uint64_t keep = na::policy_evict_last(), stream = na::policy_evict_first();
     const Level L = make_level<F>(sl[level], dtable);
     float* tb = const_cast<float*>(L.base) + sub * 4;
-    const int64_t cta_base = (int64_t)blockIdx.x * kAxisPoints;
+    const int64_t cta_base = (int64_t)point_block * kAxisPoints;
     // (measured and rejected, profiles/r02_hashgrid.md: prefetching the next point's loads, and a fourth resident CTA,
     //  both slow this kernel down -- it is bound by the L2's reduction throughput, more requests in flight only queue)
 #pragma unroll 1
@@ -920,20 +923,28 @@ int launch_bwd(const na_hashgrid_desc* desc, const float* x, int64_t n_points, n
             if (split < level_base) split = level_base;
             if (split > active_levels) split = active_levels;
 #endif
-            auto launch = [&](uint32_t l0, uint32_t l1, bool part, uint32_t lo, uint32_t hi) {
+            // Large batches: the leading dense levels (a few MB of gradient each, every row hit hundreds of times) are
+            // interleaved across consecutive CTAs instead of processed one after the other: 7.28 -> 7.13 ms at 2^22 x 7
+            // with levels 0-5 (4 / 6 / 8 / 12 interleaved levels: 7.14 / 7.13 / 7.16 / 9.75 ms -- hashed levels thrash the L2).
+            uint32_t il = 0;
+            if (n_points >= (1 << 21))
+                while (level_base + il < split && !desc->hashed[level_base + il] && nb * (int64_t)(il + 1) <= 0x7fffffffLL) ++il;
+            auto launch = [&](uint32_t l0, uint32_t l1, bool part, uint32_t lo, uint32_t hi, uint32_t inter = 0) {
                 if (l1 <= l0) return;
-                dim3 g((unsigned)nb, l1 - l0);
+                dim3 g(inter ? (unsigned)(nb * inter) : (unsigned)nb, inter ? 1u : l1 - l0);
                 if (tp.n == 1)
                     hashgrid_axis_bwd_kernel<1, false><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
-                                                                                   dout_tap_stride, dout_level_stride, dtable, l0, lo, hi);
+                                                                                   dout_tap_stride, dout_level_stride, dtable, l0, lo, hi, inter);
                 else if (!part)
                     hashgrid_axis_bwd_kernel<7, false><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
-                                                                                   dout_tap_stride, dout_level_stride, dtable, l0, lo, hi);
+                                                                                   dout_tap_stride, dout_level_stride, dtable, l0, lo, hi, inter);
                 else
                     hashgrid_axis_bwd_kernel<7, true><<<g, kThreads, 0, stream>>>(*desc, x, n_points, map, at, dout, dout_stride,
-                                                                                  dout_tap_stride, dout_level_stride, dtable, l0, lo, hi);
+                                                                                  dout_tap_stride, dout_level_stride, dtable, l0, lo, hi, inter);
             };
-            launch(level_base, split, false, 0u, 0xffffffffu);
+            if (il > 1) launch(level_base, level_base + il, false, 0u, 0xffffffffu, il);
+            else il = 0;
+            launch(level_base + il, split, false, 0u, 0xffffffffu);
             for (uint32_t l = split; l < active_levels; ++l) {
                 const uint32_t half = (desc->entries[l] + 1) / 2;
                 launch(l, l + 1, true, 0u, half);

@@ -95,15 +95,23 @@ def encode_taps_planes(desc, table, x, unit_map, active_levels, tap_offsets, out
 
 
 def bwd_launch_count(desc, n_points, n_taps, active_levels):
-    """Kernel launches of one backward call on the axis-factorised path (mirrors launch_bwd in csrc/hashgrid.cu): one launch
-    for the levels scattered whole, two row-range passes for each of the (at most four) finest hashed levels of a large
-    7-evaluation batch whose gradient exceeds 96 MiB."""
+    """Kernel launches of one backward call on the axis-factorised path (mirrors launch_bwd in csrc/hashgrid.cu): for a
+    large batch one launch for the leading dense levels (interleaved across CTAs), one for the other levels scattered
+    whole, two row-range passes for each of the (at most four) finest hashed levels of a 7-evaluation batch whose
+    gradient exceeds 96 MiB."""
     split = active_levels
     if n_points >= (1 << 21) and n_taps == 7:
         while split > 0 and split + 4 > active_levels and desc.hashed[split - 1] and \
                 desc.entries[split - 1] * desc.n_features * 4 > (96 << 20):
             split -= 1
-    return (1 if split > 0 else 0) + 2 * (active_levels - split)
+    dense = 0
+    if n_points >= (1 << 21):
+        while dense < split and not desc.hashed[dense]:
+            dense += 1
+    if dense <= 1:
+        dense = 0
+    whole = (1 if dense else 0) + (1 if split > dense else 0)     # interleaved dense levels, remaining whole levels
+    return whole + 2 * (active_levels - split)
 
 
 def scatter_taps_planes(desc, x, unit_map, active_levels, tap_offsets, dout, dtable):

@@ -156,6 +156,25 @@ def test_full_size_properties(default_grid, cuda_device):
         xo = x[:m] + torch.tensor(off, device=cuda_device)
         sep = hashgrid.encode_taps(desc, table_d, xo, um, 16, ((0, 0, 0),))[0]
         assert torch.equal(sep, taps[t]) or (sep - taps[t]).abs().max().item() < 1e-6
+    del taps, sep
+    # (iv) the large-batch 7-evaluation backward (>= 2^21 points: dense levels interleaved across CTAs, the four finest
+    # levels scattered in two row-range passes) equals the sum of two half-batch calls, which take the plain path
+    n2 = 1 << 21
+    g7 = torch.Generator(device=cuda_device).manual_seed(7)
+    dout7 = torch.randn(7, 16, n2, 8, device=cuda_device, generator=g7)
+    big = torch.zeros_like(table_d)
+    hashgrid.scatter_taps_planes(desc, x[:n2], um, 16, SIX_TAPS(e), dout7, big)
+    assert hashgrid.bwd_launch_count(desc, n2, 7, 16) == 10 and hashgrid.bwd_launch_count(desc, n2 // 2, 7, 16) == 1
+    halves = torch.zeros_like(table_d)
+    for h in range(2):
+        sl = slice(h * n2 // 2, (h + 1) * n2 // 2)
+        hashgrid.scatter_taps_planes(desc, x[:n2][sl], um, 16, SIX_TAPS(e), dout7[:, :, sl].contiguous(), halves)
+    scale = halves.abs().max().item()
+    assert scale > 0 and (big - halves).abs().max().item() <= 2e-5 * scale     # same terms, another order of fp32 additions
+    for l in (0, 5, 6, 11, 12, 15):      # every kind of level: interleaved dense, whole hashed, split hashed
+        lo, hi = desc.offset[l] * 8, (desc.offset[l] + desc.entries[l]) * 8
+        ref_l2 = halves[lo:hi].double().norm().item()
+        assert abs(big[lo:hi].double().norm().item() - ref_l2) <= 1e-6 * ref_l2, l
 
 
 def test_errors_are_reported(na_lib, cuda_device):
