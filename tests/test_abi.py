@@ -86,3 +86,30 @@ def test_plane_entry_point_validates_its_envelope(na_lib):
     rc = na_lib.na_sdf_head_fwd_planes(fake, 8 * 100, 128, 131, 256, fake, fake, fake, 144, None, None, 100.0, None, None, 0, None)
     assert rc != 0 and b"chunk_stride" in na_lib.na_last_error()
     assert na_lib.na_sdf_head_fwd_planes(fake, 8 * 128, 0, 131, 256, fake, fake, fake, 144, None, None, 100.0, None, None, 0, None) == 0
+
+
+def test_new_entry_points_validate_their_envelopes_without_a_gpu(na_lib):
+    """Argument checks of the round-2 entry points run before any CUDA call: wrong shapes / null pointers come back as
+    NA_ERR_INVALID with a message, never as a crash."""
+    from neuralangelo_b200 import _lib, hashgrid
+    L = _lib.lib()
+    desc = hashgrid.make_desc(16, 8, 22, 32, 1.3195079107728942)
+    one = ctypes.c_void_p(256)   # a non-null, 256-byte aligned "pointer" that is never dereferenced: validation fails first
+    rc = L.na_lattice_sdf(ctypes.byref(desc), one, one, one, one, 4, 4, 4, _lib.UnitMap(-2.0, 0.25), 16, one, one, 128, 256,
+                          one, one, 1.0, one, None)
+    assert rc == -1 and b"k0_pad" in L.na_last_error()
+    small = hashgrid.make_desc(4, 8, 10, 4, 2.0)
+    rc = L.na_lattice_sdf(ctypes.byref(small), one, one, one, one, 4, 4, 4, _lib.UnitMap(-2.0, 0.25), 4, one, one, 144, 256,
+                          one, one, 1.0, one, None)
+    assert rc == -1 and b"levels" in L.na_last_error()
+    rc = L.na_sdf_head_ws(one, 64, one, 131, 8, one, one, 144, 256, one, one, 1.0, one, None)
+    assert rc == -1 and b"exactly one" in L.na_last_error()
+    rc = L.na_pack_split_f16(one, 278, 250, 250, 278, 0, 0, 1.0, None, 288, one, one, None)
+    assert rc == -1 and b"multiple of 8" in L.na_last_error()
+    rc = L.na_ray_setup(one, one, one, 1, 8, 0, one, one, one, None, None, None, None)
+    assert rc == -1 and b"ray_setup" in L.na_last_error()
+    # launch count of the large-batch backward (mirrors launch_bwd): dense levels interleaved + whole levels + 4 x 2 passes
+    assert hashgrid.bwd_launch_count(desc, 1 << 22, 7, 16) == 10
+    assert hashgrid.bwd_launch_count(desc, 1 << 22, 1, 16) == 2
+    assert hashgrid.bwd_launch_count(desc, 1 << 16, 7, 16) == 1
+    assert hashgrid.bwd_launch_count(desc, 1 << 22, 7, 4) == 1
