@@ -1003,8 +1003,13 @@ extern "C" int na_sdf_mlp_fwd(const float* x, int64_t ldx, int64_t m, int k0, in
     P.sdf_out = sdf_out, P.feat_out = feat_out, P.ld_feat = ld_feat, P.hidden_out = hidden_out, P.ld_hidden = ld_hidden;
     const int64_t tiles = (m + kTileM - 1) / kTileM;
     const unsigned grid = (unsigned)(tiles < na::kNumSMs ? tiles : na::kNumSMs);
-    // SDF-only evaluation: the pipelined kernel with resident weights (NA_MLP_NO_PIPE=1: developer switch for A/B runs)
+    // SDF-only evaluation: the pipelined kernel with resident weights (developer builds with -DNA_MLP_DEV_KNOBS:
+    // NA_MLP_NO_PIPE=1 switches it off for A/B runs; the shipped library never reads the environment)
+#ifdef NA_MLP_DEV_KNOBS
     static const bool no_pipe = getenv("NA_MLP_NO_PIPE") != nullptr;
+#else
+    constexpr bool no_pipe = false;
+#endif
     const uint32_t pipe_smem = pipe_smem_bytes(k0_pad, n);
     const int rounds = k0 / 32;
     if (!no_pipe && n_layers == 1 && n % 128 == 0 && k0 - 32 * rounds <= kPipeTail && pipe_kernel_for<false>(rounds) &&
