@@ -80,3 +80,26 @@ def test_block_sharding_is_round_robin_without_padding():
     # 4096 blocks (res 2048 / block 128) over 8 ranks: 512 each, block idx = rank (mod 8), as DistributedSampler(shuffle=False)
     s8 = [parallel.shard_indices(4096, r, 8) for r in range(8)]
     assert all(len(s) == 512 for s in s8) and s8[3][:3] == [3, 11, 19]
+
+
+def test_flat_bucket_puts_every_parameter_on_a_256_byte_boundary():
+    """FusedAdamW's bucket: each small parameter (and its gradient view) starts on a multiple of 64 floats -- the library
+    GEMMs that still read biases / weights on the training path pick their vectorised kernels only for 16-byte aligned
+    operands -- the views alias the bucket, and the padding between parameters is zero."""
+    import torch
+    from neuralangelo_b200.optim import FusedAdamW
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(7, 5), torch.nn.Linear(5, 3), torch.nn.Linear(3, 257))
+    before = [p.detach().clone() for p in model.parameters()]
+    opt = FusedAdamW(model)
+    base_p, base_g = opt.flat_p.data_ptr(), opt.flat_g.data_ptr()
+    covered = torch.zeros(opt.flat_p.numel(), dtype=torch.bool)
+    for p, ref, g in zip(model.parameters(), before, opt._grad_views):
+        off = (p.data_ptr() - base_p) // 4
+        assert off % 64 == 0 and (g.data_ptr() - base_g) // 4 == off
+        assert torch.equal(p.detach(), ref)                      # values moved into the bucket unchanged
+        covered[off:off + p.numel()] = True
+    assert opt.flat_p.numel() % 64 == 0 and float(opt.flat_p[~covered].abs().max()) == 0.0
+    model[0].bias.data.fill_(3.0)                                # the parameter IS the bucket
+    off = (model[0].bias.data_ptr() - base_p) // 4
+    assert torch.equal(opt.flat_p[off:off + 5], torch.full((5,), 3.0))
